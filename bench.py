@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py — HGA channel-samples/s on B200 (BASELINE.json metric), one process per GPU.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload k2|k4|k1]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+A step = one pass of the hot path (IIR cascade + framing + log-power + z-score) over one resident recording per rank
+(default K2: 128 ch x 1 h @ 1 kHz, float64, 3.69 GB > L2, so no L2 flush is needed between steps).  Ranks hold
+different recordings (weak scaling, no data-path collective); the day-baseline (mu, sigma) are computed before the timed
+region from a 60 s baseline prefix per rank, combined over ranks by an NCCL all-gather + fixed-order Chan merge.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOADS = {  # name: (fs, channels, seconds)
+    "k1": (1000, 128, 60),
+    "k2": (1000, 128, 3600),
+    "k4": (2000, 1024, 600),
+}
+METRIC = "hga_channel_samples_per_s"
+UNIT = "channel-samples/s"
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 7:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's own CPU composition (scipy sosfilt x2 -> compiled reference extension
+# compute_log_power_features -> numpy z-score), see oracle/.
+# ----------------------------------------------------------------------------------------------------------------------
+def _ref_worker(args):
+    x, fs, mu, sigma = args
+    from oracle import build_ref, hga_oracle as O
+    ref = build_ref.load()
+    ex = O.HighGammaExtractor(fs, x.shape[1], log_power=(ref.compute_log_power_features if ref is not None
+                                                          else O.compute_log_power_features_fast))
+    f = ex.extract_features(x)
+    return (f - mu) / sigma
+
+
+def reference_rate(fs: int, C: int, seconds: int, procs: int, budget_s: float, min_reps: int = 1):
+    """channel-samples/s of the reference composition on `procs` host processes (channels split across them)."""
+    from oracle import build_ref, hga_oracle as O
+    kind = "reference" if build_ref.load() is not None else "port"
+    x = O.synthetic_ecog(fs * seconds, C, fs, "white")
+    procs = max(1, min(procs, C))
+    blocks = np.array_split(np.arange(C), procs)
+    jobs = [(np.ascontiguousarray(x[:, b]), fs, np.full(len(b), 3.0), np.full(len(b), 0.4)) for b in blocks]
+    times = []
+    if procs == 1:
+        t_end = time.perf_counter() + budget_s
+        while len(times) < min_reps or time.perf_counter() < t_end:
+            t0 = time.perf_counter()
+            _ref_worker(jobs[0])
+            times.append(time.perf_counter() - t0)
+            if len(times) >= 50:
+                break
+    else:
+        import multiprocessing as mp
+        with mp.get_context("fork").Pool(procs) as pool:
+            pool.map(_ref_worker, jobs)  # warm the workers
+            t_end = time.perf_counter() + budget_s
+            while len(times) < min_reps or time.perf_counter() < t_end:
+                t0 = time.perf_counter()
+                pool.map(_ref_worker, jobs)
+                times.append(time.perf_counter() - t0)
+                if len(times) >= 50:
+                    break
+    best = float(np.median(times))
+    return fs * seconds * C / best, kind, f"{C} ch x {seconds} s @ {fs} Hz white float64, median of {len(times)} runs"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    fs, C, secs = WORKLOADS[args.workload]
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    sample_s = 120 if fs * C <= 128000 else 15
+    from oracle import hga_oracle as O
+    x_fs = fs
+    times = []
+    # steps/warmup honoured: each step = one bounded sample across all cores
+    import multiprocessing as mp
+    from oracle import build_ref
+    kind = "reference" if build_ref.load() is not None else "port"
+    x = O.synthetic_ecog(fs * sample_s, C, fs, "white")
+    procs = max(1, min(cores, C))
+    blocks = np.array_split(np.arange(C), procs)
+    jobs = [(np.ascontiguousarray(x[:, b]), x_fs, np.full(len(b), 3.0), np.full(len(b), 0.4)) for b in blocks]
+    with mp.get_context("fork").Pool(procs) as pool:
+        for _ in range(max(1, args.warmup)):
+            pool.map(_ref_worker, jobs)
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            pool.map(_ref_worker, jobs)
+            times.append(time.perf_counter() - t0)
+    ms = 1e3 * float(np.mean(times))
+    value = fs * sample_s * C / (ms / 1e3)
+    sample = f"{C} ch x {sample_s} s @ {fs} Hz white float64 per step, channels split over {procs} processes"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": {"workload": workload_name(args.workload), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_name(w):
+    fs, C, secs = WORKLOADS[w]
+    return f"{w}: {C} ch x {secs} s @ {fs} Hz float64, band-pass+notch cascade, 50ms/10ms log-power, z-score"
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from delayed_speech_synthesis_b200 import _lib
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    from delayed_speech_synthesis_b200.ops import ChannelStats
+    from delayed_speech_synthesis_b200 import corpus
+
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the HGA path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    fs, C, secs = WORKLOADS[args.workload]
+    T = fs * secs
+    hbm_peak, peak_src = peaks()
+
+    # synthetic recording, generated on the device (Philox), distinct per rank
+    g = torch.Generator(device=dev)
+    g.manual_seed(20241104 + rank)
+    x = torch.empty((T, C), dtype=torch.float64, device=dev)
+    step_rows = max(1, (1 << 27) // C)
+    for r0 in range(0, T, step_rows):
+        x[r0:r0 + step_rows].normal_(generator=g)
+    x += (5.0 * torch.sin(2 * torch.pi * 120.0 * torch.arange(T, device=dev, dtype=torch.float64) / fs)).unsqueeze(1)
+
+    eng = HgaEngine(fs, C, precision=args.precision, device=local)
+    # day baseline from the first 60 s of every rank's recording, combined over ranks
+    base = eng.extract_offline(x[: 60 * fs])
+    st = ChannelStats(C, local).update(base)
+    t0 = time.perf_counter()
+    acc = corpus.gather_accumulators(st.acc) if world > 1 else st.acc.unsqueeze(0)
+    merged = ChannelStats(C, local).merge(acc)
+    mu, sigma = merged.finalize(as_numpy=False)
+    torch.cuda.synchronize()
+    stats_ms = 1e3 * (time.perf_counter() - t0)
+
+    F = eng.num_frames(T)
+    out = torch.empty((F, C), dtype=torch.float64, device=dev)
+
+    def step():
+        eng.extract_offline(x, None, mu, sigma, out=out)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    l0 = lib.hga_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+    launches = lib.hga_launch_count() - l0
+    ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * C * T / (ms / 1e3)
+
+    # ---- end to end through the host-buffer C-ABI call: pinned host input, host output, copies inside the timed region
+    e2e = None
+    try:
+        xh = torch.empty((T, C), dtype=torch.float64, pin_memory=True)
+        xh.copy_(x)
+        oh = torch.empty((F, C), dtype=torch.float64, pin_memory=True)
+        mu_h, sg_h = mu.cpu().numpy(), sigma.cpu().numpy()
+        xn, on = xh.numpy(), oh.numpy()
+        n_e2e = max(2, min(args.steps, 5))
+        eng.extract_offline(xn, None, mu_h, sg_h, out=on)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            eng.extract_offline(xn, None, mu_h, sg_h, out=on)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / n_e2e
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e_ok = bool(torch.equal(oh.to(dev), out))
+        e2e = {"value": world * C * T / dt, "unit": UNIT, "h2d_bytes_per_step": int(T * C * 8), "d2h_bytes_per_step": int(F * C * 8),
+               "ms_per_step": 1e3 * dt, "matches_device_result": e2e_ok}
+        del xh, oh
+    except Exception as exc:  # report, do not hide
+        e2e = {"value": None, "unit": UNIT, "error": repr(exc)}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    hop = eng.hop
+    bytes_per = 8.0 + 8.0 / hop
+    achieved = C * T * bytes_per / (ms / 1e3) / 1e9  # per rank: one launch per step
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, kind, sample = reference_rate(fs, C, 60, 1, budget_s=12.0)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample}
+    traffic = None
+    tp = ROOT / "profiles" / "traffic.json"
+    if tp.exists():
+        traffic = json.loads(tp.read_text()).get(args.workload)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": workload_name(args.workload), "precision": args.precision, "warmup_samples": eng.warmup,
+                   "l2": "input 3.69 GB per step > 126 MB L2 (no flush needed)" if args.workload != "k1" else "k1 fits L2",
+                   "sessions_per_rank": 1, "stats_exchange_ms": stats_ms},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                     "traffic": traffic, "peak_source": peak_src, "bytes_per_channel_sample": bytes_per,
+                     "kernel_ms": ms},
+        "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="k2", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="f64", choices=["f64", "exact"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,822 @@
+// hga_api.cu — the C ABI of libhga_b200.so (include/hga_b200.h) over the sm_100a kernels.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -shared -Xcompiler -fPIC (see __graft_entry__.py)
+#include "../../include/hga_b200.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <complex>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "hga_common.cuh"
+#include "hga_kernels_exact.cuh"
+#include "hga_kernels_fused.cuh"
+#include "hga_kernels_pipe.cuh"
+
+using namespace hga;
+
+// ------------------------------------------------------------------------------------------------ errors / misc
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CU(call)                                                                                        \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) return fail(HGA_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                       __FILE__, __LINE__);                                             \
+  } while (0)
+#define LAUNCHED()                                                                                       \
+  do {                                                                                                   \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                                                  \
+    cudaError_t e_ = cudaGetLastError();                                                                 \
+    if (e_ != cudaSuccess) return fail(HGA_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), \
+                                       __FILE__, __LINE__);                                              \
+  } while (0)
+
+extern "C" const char* hga_last_error(void) { return g_err.c_str(); }
+extern "C" int hga_abi_version(void) { return HGA_ABI_VERSION; }
+extern "C" int64_t hga_launch_count(void) { return g_launches.load(); }
+extern "C" int hga_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// Growable device buffer.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return HGA_OK;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(HGA_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    }
+    cap = bytes;
+    return HGA_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T>
+  T* as() const { return static_cast<T*>(p); }
+};
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return HGA_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(HGA_ERR_NOMEM, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    }
+    cap = bytes;
+    return HGA_OK;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <class T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+// ------------------------------------------------------------------------------------------------ cascade set-up
+// Fill a Cascade from one or two scipy SOS matrices (rows [b0 b1 b2 a0 a1 a2], a0 == 1).
+static int build_cascade(Cascade& q, const double* sos_a, int na, const double* zi_a, const double* sos_b, int nb,
+                         const double* zi_b) {
+  if (na < 0 || nb < 0 || na + nb < 1 || na + nb > kMaxSec) return fail(HGA_ERR_INVALID, "bad section count %d+%d", na, nb);
+  memset(&q, 0, sizeof q);
+  q.ns = na + nb;
+  q.ns_a = na;
+  q.unit = 1;
+  for (int s = 0; s < q.ns; ++s) {
+    const double* r = s < na ? sos_a + 6 * s : sos_b + 6 * (s - na);
+    const double* z = s < na ? (zi_a ? zi_a + 2 * s : nullptr) : (zi_b ? zi_b + 2 * (s - na) : nullptr);
+    if (r[3] != 1.0) return fail(HGA_ERR_INVALID, "section %d: a0 must be 1 (got %g)", s, r[3]);
+    q.b0[s] = r[0]; q.b1[s] = r[1]; q.b2[s] = r[2]; q.a1[s] = r[4]; q.a2[s] = r[5];
+    q.zi0[s] = z ? z[0] : 0.0;
+    q.zi1[s] = z ? z[1] : 0.0;
+    if (r[0] == r[2] && r[0] != 0.0) {
+      q.g[s] = r[0];
+      q.b1u[s] = r[1] / r[0];
+      if (r[0] != 1.0) q.has_gain |= 1u << s;
+    } else {
+      q.unit = 0;
+    }
+  }
+  for (int s = q.ns; s < kMaxSec; ++s) q.g[s] = 1.0;
+  return HGA_OK;
+}
+// "standard" layout the fully specialised kernels assume: 8 + 8 sections, gains only at sections 0 and 8.
+static bool is_unit_std(const Cascade& q) {
+  return q.unit && q.ns == 16 && q.ns_a == 8 && (q.has_gain & ~0x101u) == 0;
+}
+// Largest pole radius of the cascade (roots of z^2 + a1 z + a2).
+static double max_pole_radius(const Cascade& q) {
+  double r = 0.0;
+  for (int s = 0; s < q.ns; ++s) {
+    const double disc = q.a1[s] * q.a1[s] - 4.0 * q.a2[s];
+    if (disc < 0) r = std::max(r, std::sqrt(std::fabs(q.a2[s])));
+    else r = std::max(r, (std::fabs(q.a1[s]) + std::sqrt(disc)) / 2.0);
+  }
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------------ the handle
+struct hga_handle {
+  hga_config cfg;
+  Cascade q;
+  int n_sm = 0;
+  int warmup = 0;
+  int overlap = 0;   // L - hop
+  int nb = 0;        // L / hop when L % hop == 0, else 0 (fused kernels unavailable)
+  int cap_rows = 0;  // rows of the streaming frame buffer
+  // streaming state (device)
+  DevBuf state, state2;        // (ns, 2, C); state2 = ping-pong partner for bulk pushes
+  DevBuf framebuf, framebuf2;  // (cap_rows, C): [remainder | new rows]
+  int first_frame = 1;
+  // scratch
+  DevBuf work, segs, ybuf, stats_part, seg_state, seg_rem;
+  std::vector<Work> work_host;
+  std::vector<Segment> segs_host;
+  std::vector<int64_t> plan_key;  // seg_start/len/out_row of the cached plan
+  int plan_variant = -1;
+  // host-buffer paths
+  DevBuf xdev, outdev, mudev, sigdev;
+  PinBuf pin_in, pin_out;
+  std::vector<double> mu_cache, sig_cache;
+  bool musig_valid = false;
+  cudaStream_t s_own = nullptr, s_copy = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::vector<cudaEvent_t> slab_ev;
+  int timing = 0;
+  bool timed = false;
+};
+
+static int tile_zi(hga_handle* h, cudaStream_t st) {
+  const int C = h->cfg.n_channels, ns = h->q.ns;
+  std::vector<double> z((size_t)ns * 2 * C);
+  for (int s = 0; s < ns; ++s)
+    for (int c = 0; c < C; ++c) {
+      z[((size_t)2 * s) * C + c] = h->q.zi0[s];
+      z[((size_t)2 * s + 1) * C + c] = h->q.zi1[s];
+    }
+  CU(cudaMemcpyAsync(h->state.p, z.data(), z.size() * 8, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(h->framebuf.p, 0, (size_t)h->cap_rows * C * 8, st));
+  CU(cudaStreamSynchronize(st));  // z is a stack-owned vector
+  h->first_frame = 1;
+  return HGA_OK;
+}
+
+extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
+  if (!cfg || !out) return fail(HGA_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (cfg->abi_version != HGA_ABI_VERSION) return fail(HGA_ERR_INVALID, "ABI version %d != %d", cfg->abi_version, HGA_ABI_VERSION);
+  if (cfg->n_channels < 1 || cfg->frame_len < 1 || cfg->hop < 1 || cfg->frame_len < cfg->hop || cfg->fs < 1)
+    return fail(HGA_ERR_INVALID, "bad geometry: C=%d L=%d hop=%d fs=%d", cfg->n_channels, cfg->frame_len, cfg->hop, cfg->fs);
+  if (cfg->n_sections_bp < 1 || cfg->n_sections_bp > HGA_MAX_SECTIONS || cfg->n_sections_notch < 0 ||
+      cfg->n_sections_notch > HGA_MAX_SECTIONS)
+    return fail(HGA_ERR_INVALID, "bad section counts %d/%d", cfg->n_sections_bp, cfg->n_sections_notch);
+  if (cfg->precision != HGA_PREC_EXACT && cfg->precision != HGA_PREC_F64) return fail(HGA_ERR_INVALID, "bad precision %d", cfg->precision);
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  if (cfg->device < 0 || cfg->device >= hga_device_count()) return fail(HGA_ERR_INVALID, "bad device %d", cfg->device);
+  CU(cudaSetDevice(cfg->device));
+  hga_handle* h = new hga_handle();
+  h->cfg = *cfg;
+  int rc = build_cascade(h->q, cfg->sos_bp, cfg->n_sections_bp, cfg->zi_bp, cfg->sos_notch, cfg->n_sections_notch, cfg->zi_notch);
+  if (rc) { delete h; return rc; }
+  cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, cfg->device);
+  h->overlap = cfg->frame_len - cfg->hop;
+  h->nb = (cfg->frame_len % cfg->hop == 0 && cfg->frame_len / cfg->hop <= kMaxBlocksPerFrame) ? cfg->frame_len / cfg->hop : 0;
+  const double r = max_pole_radius(h->q);
+  if (r >= 1.0) { delete h; return fail(HGA_ERR_INVALID, "unstable filter: pole radius %g", r); }
+  if (cfg->warmup > 0) h->warmup = cfg->warmup;
+  else {
+    const double tol = cfg->warmup_tol > 0 ? cfg->warmup_tol : 1e-10;
+    h->warmup = r > 0 ? (int)std::ceil(std::log(tol) / std::log(r)) : 1;
+  }
+  h->warmup = std::max(h->warmup, h->overlap);
+  h->warmup = (h->warmup + cfg->hop - 1) / cfg->hop * cfg->hop;
+  const int max_push = cfg->max_push_rows > 0 ? cfg->max_push_rows : 4096;
+  h->cap_rows = std::max(cfg->frame_len, h->overlap + max_push);
+  const int C = cfg->n_channels;
+  if ((rc = h->state.reserve((size_t)h->q.ns * 2 * C * 8)) || (rc = h->framebuf.reserve((size_t)h->cap_rows * C * 8)) ||
+      (rc = h->state2.reserve((size_t)h->q.ns * 2 * C * 8)) || (rc = h->framebuf2.reserve((size_t)h->cap_rows * C * 8))) {
+    hga_destroy(h);
+    return rc;
+  }
+  cudaStreamCreateWithFlags(&h->s_own, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking);
+  cudaEventCreate(&h->ev0);
+  cudaEventCreate(&h->ev1);
+  if ((rc = tile_zi(h, h->s_own))) { hga_destroy(h); return rc; }
+  *out = h;
+  return HGA_OK;
+}
+
+extern "C" int hga_destroy(hga_handle* h) {
+  if (!h) return HGA_OK;
+  cudaSetDevice(h->cfg.device);
+  for (DevBuf* b : {&h->state, &h->framebuf, &h->state2, &h->framebuf2, &h->work, &h->segs, &h->ybuf, &h->stats_part, &h->seg_state, &h->seg_rem,
+                    &h->xdev, &h->outdev, &h->mudev, &h->sigdev})
+    b->release();
+  h->pin_in.release();
+  h->pin_out.release();
+  for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->s_own) cudaStreamDestroy(h->s_own);
+  if (h->s_copy) cudaStreamDestroy(h->s_copy);
+  delete h;
+  return HGA_OK;
+}
+
+extern "C" int hga_reset(hga_handle* h, void* stream) {
+  if (!h) return fail(HGA_ERR_INVALID, "null handle");
+  CU(cudaSetDevice(h->cfg.device));
+  return tile_zi(h, (cudaStream_t)stream);
+}
+extern "C" int hga_warmup(const hga_handle* h) { return h ? h->warmup : 0; }
+extern "C" int hga_set_timing(hga_handle* h, int32_t enable) {
+  if (!h) return fail(HGA_ERR_INVALID, "null handle");
+  h->timing = enable;
+  h->timed = false;
+  return HGA_OK;
+}
+extern "C" double hga_last_kernel_ms(hga_handle* h) {
+  if (!h || !h->timed) return -1.0;
+  float ms = 0;
+  if (cudaEventSynchronize(h->ev1) != cudaSuccess || cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) {
+    cudaGetLastError();
+    return -1.0;
+  }
+  return ms;
+}
+extern "C" int64_t hga_num_frames(const hga_handle* h, int64_t rows) {
+  if (!h || rows < h->cfg.frame_len) return 0;
+  return (rows - h->cfg.frame_len) / h->cfg.hop + 1;
+}
+
+// ------------------------------------------------------------------------------------------------ offline path
+// Build the time-chunk work list.  Cost model: items run `slots` warps at a time, each costing (chunk + warm-up)
+// samples; pick the chunk length that minimises waves * (chunk + warmup).
+static void plan_chunks(hga_handle* h, int n_seg, const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
+                        int64_t slots_items, bool allow_chunking) {
+  const int hop = h->cfg.hop, K = h->warmup, nb = h->nb;
+  int64_t total = 0, maxT = 0;
+  for (int i = 0; i < n_seg; ++i) { total += seg_len[i]; maxT = std::max(maxT, seg_len[i]); }
+  int64_t best_Lc = (maxT + hop - 1) / hop * hop;
+  if (allow_chunking && slots_items > 0) {
+    double best = 1e300;
+    const int64_t min_Lc = std::max<int64_t>((int64_t)h->cfg.frame_len * 4, 64 * hop);
+    for (int64_t n = 1; n <= 1 << 20; n = n < 64 ? n + 1 : n + n / 16) {
+      int64_t Lc = ((total + n - 1) / n + hop - 1) / hop * hop;
+      if (Lc < min_Lc) break;
+      int64_t items = 0;
+      for (int i = 0; i < n_seg; ++i) items += (seg_len[i] + Lc - 1) / Lc;
+      const int64_t waves = (items + slots_items - 1) / slots_items;
+      const double per = (double)std::min(Lc, maxT) + (items > n_seg ? (double)K : 0.0);
+      const double cost = waves * per;
+      if (cost < best * 0.999) { best = cost; best_Lc = Lc; }
+    }
+  }
+  h->work_host.clear();
+  h->segs_host.clear();
+  for (int i = 0; i < n_seg; ++i) {
+    const int64_t T = seg_len[i];
+    h->segs_host.push_back(Segment{seg_start[i], T, out_row[i]});
+    const int64_t n_items = std::max<int64_t>(1, (T + best_Lc - 1) / best_Lc);
+    for (int64_t k = 0; k < n_items; ++k) {
+      Work w;
+      const int64_t cs = k * best_Lc;
+      w.row0 = seg_start[i];
+      w.T = T;
+      w.t_begin = std::max<int64_t>(0, cs - K);
+      w.t_acc = std::max<int64_t>(0, cs - (int64_t)(nb - 1) * hop);
+      if (w.t_begin > w.t_acc) w.t_begin = w.t_acc;
+      w.last = k == n_items - 1;
+      w.t_end = w.last ? T : cs + best_Lc;
+      w.out_row0 = out_row[i];
+      w.seg = i;
+      h->work_host.push_back(w);
+    }
+  }
+}
+
+static int upload_plan(hga_handle* h, cudaStream_t st) {
+  int rc;
+  if ((rc = h->work.reserve(std::max<size_t>(1, h->work_host.size()) * sizeof(Work)))) return rc;
+  if ((rc = h->segs.reserve(std::max<size_t>(1, h->segs_host.size()) * sizeof(Segment)))) return rc;
+  if (!h->work_host.empty())
+    CU(cudaMemcpyAsync(h->work.p, h->work_host.data(), h->work_host.size() * sizeof(Work), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(h->segs.p, h->segs_host.data(), h->segs_host.size() * sizeof(Segment), cudaMemcpyHostToDevice, st));
+  CU(cudaStreamSynchronize(st));  // pageable source: keep it simple and safe; plans are cached across calls
+  return HGA_OK;
+}
+
+// Which fused kernel: 0 = thread-per-(item, channel) sequential cascade, 1 = warp-pipelined.
+static int choose_variant(const hga_handle* h, int n_seg, const int64_t* seg_len) {
+  const char* env = getenv("HGA_B200_VARIANT");
+  if (env && *env) return atoi(env);
+  return pipe_supported(h->q, h->cfg.hop, h->nb) ? pipe_preferred(h->n_sm, h->cfg.n_channels, n_seg, seg_len, h->warmup) : 0;
+}
+
+template <int ARITH>
+static int launch_fused_seq(hga_handle* h, const FusedArgs& a, cudaStream_t st) {
+  const int cg = (a.C + 31) / 32;
+  const int64_t warps = (int64_t)a.n_work * cg;
+  const unsigned grid = (unsigned)((warps + 3) / 4);
+  if (a.hop == 10) k_hga_fused_seq<ARITH, 10><<<grid, 128, 0, st>>>(h->q, a);
+  else if (a.hop == 20) k_hga_fused_seq<ARITH, 20><<<grid, 128, 0, st>>>(h->q, a);
+  else k_hga_fused_seq<ARITH, 0><<<grid, 128, 0, st>>>(h->q, a);
+  LAUNCHED();
+  return HGA_OK;
+}
+
+static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int n_seg, const int64_t* seg_start,
+                               const int64_t* seg_len, const int64_t* out_row, const double* mu, const double* sigma,
+                               double* out, int64_t ldo, cudaStream_t st, double* state_out, double* rem_out,
+                               const double* state_in = nullptr, const double* rem_in = nullptr, bool allow_short = false) {
+  const int C = h->cfg.n_channels, L = h->cfg.frame_len, hop = h->cfg.hop;
+  if (n_seg < 1) return HGA_OK;
+  if ((mu == nullptr) != (sigma == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
+  for (int i = 0; i < n_seg; ++i)
+    if (seg_len[i] < L && !allow_short) return fail(HGA_ERR_INVALID, "segment %d has %lld rows < frame_len %d", i, (long long)seg_len[i], L);
+  int rc;
+  const bool fused = h->cfg.precision == HGA_PREC_F64 && h->nb > 0;
+  // plan (cached on the segment table)
+  std::vector<int64_t> key;
+  key.reserve(3 * (size_t)n_seg + 1);
+  key.insert(key.end(), seg_start, seg_start + n_seg);
+  key.insert(key.end(), seg_len, seg_len + n_seg);
+  key.insert(key.end(), out_row, out_row + n_seg);
+  const int variant = fused ? choose_variant(h, n_seg, seg_len) : -2;
+  if (key != h->plan_key || variant != h->plan_variant) {
+    const int cg = (C + 31) / 32;
+    int64_t slots = 0;
+    if (variant == 0) slots = std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
+    else if (variant == 1) slots = pipe_item_slots(h->n_sm, C);
+    plan_chunks(h, n_seg, seg_start, seg_len, out_row, slots, fused);
+    if ((rc = upload_plan(h, st))) return rc;
+    h->plan_key = key;
+    h->plan_variant = variant;
+  }
+  if (fused) {
+    FusedArgs a{x, ldx, h->work.as<Work>(), (int)h->work_host.size(), C, L, hop, h->nb, h->cfg.eps, mu, sigma, out, ldo, state_in, rem_in, state_out, rem_out};
+    if (h->timing) CU(cudaEventRecord(h->ev0, st));
+    if (variant == 1) rc = launch_pipe(h->q, a, h->n_sm, st);
+    else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, st);
+    else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, st);
+    else rc = launch_fused_seq<kFused>(h, a, st);
+    if (rc) return rc;
+    if (variant == 1) LAUNCHED();
+    if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; }
+    return HGA_OK;
+  }
+  // exact: filtered rows to scratch (same row indexing as x, compacted to the span used), then row-order windows
+  int64_t lo = INT64_MAX, hi = 0, maxF = 0;
+  for (int i = 0; i < n_seg; ++i) {
+    lo = std::min(lo, seg_start[i]);
+    hi = std::max(hi, seg_start[i] + seg_len[i]);
+    maxF = std::max(maxF, (seg_len[i] - L) / hop + 1);
+  }
+  if ((rc = h->ybuf.reserve((size_t)(hi - lo) * C * 8))) return rc;
+  double* y = h->ybuf.as<double>() - lo * C;  // y row r <-> x row r
+  const int cg = (C + 31) / 32;
+  const unsigned grid = (unsigned)(((int64_t)n_seg * cg + 3) / 4);
+  if (h->timing) CU(cudaEventRecord(h->ev0, st));
+  k_iir_seq<kExact><<<grid, 128, 0, st>>>(h->q, x, ldx, y, C, h->segs.as<Segment>(), Segment{}, n_seg, C, nullptr, state_out);
+  LAUNCHED();
+  if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; }
+  if (n_seg > 65535) return fail(HGA_ERR_UNSUPPORTED, "more than 65535 segments per call");
+  dim3 g2((unsigned)cg, (unsigned)((maxF + 7) / 8), (unsigned)n_seg);
+  k_frames_seq<<<g2, 256, 0, st>>>(y, C, 0, h->segs.as<Segment>(), Segment{}, n_seg, C, maxF, L, hop, nullptr, nullptr, h->cfg.eps, mu, sigma, out, ldo);
+  LAUNCHED();
+  if (rem_out) {
+    for (int i = 0; i < n_seg; ++i)
+      CU(cudaMemcpy2DAsync(rem_out + (size_t)i * h->overlap * C, (size_t)C * 8, y + (seg_start[i] + seg_len[i] - h->overlap) * C,
+                           (size_t)C * 8, (size_t)C * 8, h->overlap, cudaMemcpyDeviceToDevice, st));
+  }
+  return HGA_OK;
+}
+
+extern "C" int hga_extract_offline(hga_handle* h, const double* x_dev, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
+                                   const int64_t* seg_len, const int64_t* out_row, const double* mu_dev, const double* sigma_dev,
+                                   double* out_dev, int64_t ldo, void* stream) {
+  if (!h || !x_dev || !out_dev || !seg_start || !seg_len || !out_row) return fail(HGA_ERR_INVALID, "null argument");
+  if (ldx < h->cfg.n_channels || ldo < h->cfg.n_channels) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  CU(cudaSetDevice(h->cfg.device));
+  return extract_offline_dev(h, x_dev, ldx, n_segments, seg_start, seg_len, out_row, mu_dev, sigma_dev, out_dev, ldo,
+                             (cudaStream_t)stream, nullptr, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------ streaming path
+// Frame-buffer geometry of the next push of n rows (WarmStartFrameBuffer.insert cases 1-3, hga_optimized.pyx:96-131).
+struct PushGeom {
+  int y_row0, zero_rows, rows_total;
+  int64_t frames;
+};
+static PushGeom push_geom(const hga_handle* h, int64_t n) {
+  const int L = h->cfg.frame_len, hop = h->cfg.hop;
+  PushGeom g;
+  if (h->first_frame && n >= L) g = {0, 0, (int)n, 0};                               // case 1
+  else if (h->first_frame) g = {(int)(L - n), (int)(L - n), L, 0};                   // case 2
+  else g = {h->overlap, 0, (int)(h->overlap + n), 0};                                // case 3
+  g.frames = g.rows_total >= L ? (g.rows_total - L) / hop + 1 : 0;
+  return g;
+}
+extern "C" int64_t hga_stream_frames(const hga_handle* h, int64_t n) { return h && n > 0 ? push_geom(h, n).frames : 0; }
+
+// Pushes larger than kBulkRows go through the throughput kernels with the handle's state as initial condition:
+// thread-per-channel k_stream_push is a latency path.
+constexpr int64_t kBulkRows = 1024;
+static int bulk_push(hga_handle* h, const double* x, int64_t n, int64_t ldx, const double* mu, const double* sigma, double* out,
+                     int64_t ldo, int64_t* n_frames, cudaStream_t st, const PushGeom& g) {
+  const int C = h->cfg.n_channels, L = h->cfg.frame_len, hop = h->cfg.hop, ov = h->overlap;
+  const bool first = h->first_frame != 0;
+  int rc;
+  if (h->cfg.precision == HGA_PREC_F64 && h->nb > 0) {
+    // [remainder ; y] framing == fused kernel with (nb-1) preloaded hop blocks; frame w of the buffer is emitted when new
+    // block w closes, i.e. (nb-1) rows later than for a fresh stream: shift the output origin instead.
+    const int64_t s0 = 0, o0 = 0;
+    double* out_shift = first ? out : out + (int64_t)(h->nb - 1) * ldo;
+    rc = extract_offline_dev(h, x, ldx, 1, &s0, &n, &o0, mu, sigma, out_shift, ldo, st, h->state2.as<double>(), h->framebuf2.as<double>(),
+                             first ? nullptr : h->state.as<double>(), first ? nullptr : h->framebuf.as<double>(), /*allow_short=*/true);
+    if (rc) return rc;
+    std::swap(h->state, h->state2);
+    std::swap(h->framebuf, h->framebuf2);
+  } else {
+    if ((rc = h->ybuf.reserve((size_t)(ov + n) * C * 8))) return rc;
+    double* yb = h->ybuf.as<double>();
+    if (!first && ov) CU(cudaMemcpyAsync(yb, h->framebuf.p, (size_t)ov * C * 8, cudaMemcpyDeviceToDevice, st));
+    const int cg = (C + 31) / 32;
+    k_iir_seq<kExact><<<(cg + 3) / 4, 128, 0, st>>>(h->q, x, ldx, yb + (int64_t)g.y_row0 * C, C, nullptr, Segment{0, n, 0}, 1, C,
+                                                     h->state.as<double>(), h->state.as<double>());
+    LAUNCHED();
+    if (g.frames > 0) {
+      if ((rc = hga_log_power(h->cfg.device, yb, g.rows_total, 0, C, C, g.frames, L, hop, nullptr, nullptr, h->cfg.eps, mu, sigma, out, ldo, st)))
+        return rc;
+    }
+    if (ov) CU(cudaMemcpyAsync(h->framebuf.p, yb + (int64_t)(g.rows_total - ov) * C, (size_t)ov * C * 8, cudaMemcpyDeviceToDevice, st));
+  }
+  h->first_frame = 0;
+  if (n_frames) *n_frames = g.frames;
+  return HGA_OK;
+}
+
+static int stream_push_dev(hga_handle* h, const double* x, int64_t n, int64_t ldx, const double* mu, const double* sigma,
+                           double* out, int64_t ldo, int64_t* n_frames, cudaStream_t st) {
+  const int C = h->cfg.n_channels;
+  if (n < 1) return fail(HGA_ERR_INVALID, "push of %lld rows", (long long)n);
+  if (n <= kBulkRows && n + h->overlap > h->cap_rows) return fail(HGA_ERR_INVALID, "push of %lld rows exceeds max_push_rows", (long long)n);
+  if ((mu == nullptr) != (sigma == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
+  const PushGeom g = push_geom(h, n);
+  if (n > kBulkRows && !(h->first_frame && n < h->cfg.frame_len)) return bulk_push(h, x, n, ldx, mu, sigma, out, ldo, n_frames, st, g);
+  k_stream_push<<<(C + 31) / 32, 32, 0, st>>>(h->q, x, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
+                                              g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
+                                              h->cfg.eps, mu, sigma, out, ldo);
+  LAUNCHED();
+  h->first_frame = 0;
+  if (n_frames) *n_frames = g.frames;
+  return HGA_OK;
+}
+
+extern "C" int hga_stream_push(hga_handle* h, const double* x_dev, int64_t n, int64_t ldx, const double* mu_dev,
+                               const double* sigma_dev, double* out_dev, int64_t ldo, int64_t* n_frames, void* stream) {
+  if (!h || !x_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (ldx < h->cfg.n_channels || ldo < h->cfg.n_channels) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  CU(cudaSetDevice(h->cfg.device));
+  return stream_push_dev(h, x_dev, n, ldx, mu_dev, sigma_dev, out_dev, ldo, n_frames, (cudaStream_t)stream);
+}
+
+// mu/sigma host vectors are cached on the device; re-uploaded only when their contents change.
+static int sync_musigma(hga_handle* h, const double* mu, const double* sigma, cudaStream_t st, const double** mu_d,
+                        const double** sig_d) {
+  *mu_d = *sig_d = nullptr;
+  if ((mu == nullptr) != (sigma == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
+  if (!mu) return HGA_OK;
+  const int C = h->cfg.n_channels;
+  int rc;
+  if ((rc = h->mudev.reserve((size_t)C * 8)) || (rc = h->sigdev.reserve((size_t)C * 8))) return rc;
+  if (!h->musig_valid || memcmp(h->mu_cache.data(), mu, (size_t)C * 8) || memcmp(h->sig_cache.data(), sigma, (size_t)C * 8)) {
+    h->mu_cache.assign(mu, mu + C);
+    h->sig_cache.assign(sigma, sigma + C);
+    CU(cudaMemcpyAsync(h->mudev.p, h->mu_cache.data(), (size_t)C * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->sigdev.p, h->sig_cache.data(), (size_t)C * 8, cudaMemcpyHostToDevice, st));
+    h->musig_valid = true;
+  }
+  *mu_d = h->mudev.as<double>();
+  *sig_d = h->sigdev.as<double>();
+  return HGA_OK;
+}
+
+extern "C" int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t n, int64_t ldx, const double* mu_host,
+                                    const double* sigma_host, double* out_host, int64_t ldo, int64_t* n_frames) {
+  if (!h || !x_host || !out_host) return fail(HGA_ERR_INVALID, "null argument");
+  const int C = h->cfg.n_channels;
+  if (ldx < C || ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  if (n < 1 || (n <= kBulkRows && n + h->overlap > h->cap_rows))
+    return fail(HGA_ERR_INVALID, "push of %lld rows outside [1, max_push_rows]", (long long)n);
+  CU(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = h->s_own;
+  int rc;
+  const PushGeom g = push_geom(h, n);
+  if (n > kBulkRows) {  // bulk: no pinned staging, straight 2-D copies from/to the caller's buffers
+    const size_t rb = (size_t)C * 8;
+    if ((rc = h->xdev.reserve((size_t)n * rb)) || (rc = h->outdev.reserve((size_t)std::max<int64_t>(1, g.frames) * rb))) return rc;
+    const double *mu_b, *sig_b;
+    if ((rc = sync_musigma(h, mu_host, sigma_host, st, &mu_b, &sig_b))) return rc;
+    CU(cudaMemcpy2DAsync(h->xdev.p, rb, x_host, (size_t)ldx * 8, rb, (size_t)n, cudaMemcpyHostToDevice, st));
+    int64_t nfb = 0;
+    if ((rc = stream_push_dev(h, h->xdev.as<double>(), n, C, mu_b, sig_b, h->outdev.as<double>(), C, &nfb, st))) return rc;
+    if (nfb > 0) CU(cudaMemcpy2DAsync(out_host, (size_t)ldo * 8, h->outdev.p, rb, rb, (size_t)nfb, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (n_frames) *n_frames = nfb;
+    return HGA_OK;
+  }
+  const size_t in_bytes = (size_t)n * C * 8, out_bytes = (size_t)std::max<int64_t>(1, g.frames) * C * 8;
+  if ((rc = h->pin_in.reserve(in_bytes)) || (rc = h->pin_out.reserve(out_bytes)) || (rc = h->xdev.reserve(in_bytes)) ||
+      (rc = h->outdev.reserve(out_bytes)))
+    return rc;
+  const double *mu_d, *sig_d;
+  if ((rc = sync_musigma(h, mu_host, sigma_host, st, &mu_d, &sig_d))) return rc;
+  // gather rows into pinned staging (compacts ldx -> C), one H2D, one kernel, one D2H
+  double* pin = h->pin_in.as<double>();
+  if (ldx == C) memcpy(pin, x_host, in_bytes);
+  else for (int64_t r = 0; r < n; ++r) memcpy(pin + r * C, x_host + r * ldx, (size_t)C * 8);
+  CU(cudaMemcpyAsync(h->xdev.p, pin, in_bytes, cudaMemcpyHostToDevice, st));
+  int64_t nf = 0;
+  if ((rc = stream_push_dev(h, h->xdev.as<double>(), n, C, mu_d, sig_d, h->outdev.as<double>(), C, &nf, st))) return rc;
+  if (nf > 0) CU(cudaMemcpyAsync(h->pin_out.p, h->outdev.p, (size_t)nf * C * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  const double* po = h->pin_out.as<double>();
+  if (ldo == C) memcpy(out_host, po, (size_t)nf * C * 8);
+  else for (int64_t r = 0; r < nf; ++r) memcpy(out_host + r * ldo, po + r * C, (size_t)C * 8);
+  if (n_frames) *n_frames = nf;
+  return HGA_OK;
+}
+
+extern "C" int hga_get_state(hga_handle* h, double* hg_state, double* fh_state, double* remainder, int32_t* first_frame) {
+  if (!h) return fail(HGA_ERR_INVALID, "null handle");
+  CU(cudaSetDevice(h->cfg.device));
+  const size_t C = h->cfg.n_channels, na = h->q.ns_a, nb = h->q.ns - h->q.ns_a;
+  CU(cudaDeviceSynchronize());
+  if (hg_state) CU(cudaMemcpy(hg_state, h->state.p, na * 2 * C * 8, cudaMemcpyDeviceToHost));
+  if (fh_state && nb) CU(cudaMemcpy(fh_state, h->state.as<double>() + na * 2 * C, nb * 2 * C * 8, cudaMemcpyDeviceToHost));
+  if (remainder && h->overlap) CU(cudaMemcpy(remainder, h->framebuf.p, (size_t)h->overlap * C * 8, cudaMemcpyDeviceToHost));
+  if (first_frame) *first_frame = h->first_frame;
+  return HGA_OK;
+}
+extern "C" int hga_set_state(hga_handle* h, const double* hg_state, const double* fh_state, const double* remainder,
+                             const int32_t* first_frame) {
+  if (!h) return fail(HGA_ERR_INVALID, "null handle");
+  CU(cudaSetDevice(h->cfg.device));
+  const size_t C = h->cfg.n_channels, na = h->q.ns_a, nb = h->q.ns - h->q.ns_a;
+  CU(cudaDeviceSynchronize());
+  if (hg_state) CU(cudaMemcpy(h->state.p, hg_state, na * 2 * C * 8, cudaMemcpyHostToDevice));
+  if (fh_state && nb) CU(cudaMemcpy(h->state.as<double>() + na * 2 * C, fh_state, nb * 2 * C * 8, cudaMemcpyHostToDevice));
+  if (remainder && h->overlap) CU(cudaMemcpy(h->framebuf.p, remainder, (size_t)h->overlap * C * 8, cudaMemcpyHostToDevice));
+  if (first_frame) h->first_frame = *first_frame ? 1 : 0;
+  return HGA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ building blocks
+extern "C" int hga_sosfilt(int32_t device, const double* sos, int32_t n_sections, const double* x_dev, int64_t T, int32_t C,
+                           int64_t ldx, double* state_dev, double* y_dev, int64_t ldy, void* stream) {
+  if (!sos || !x_dev || !state_dev || !y_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (n_sections < 1 || n_sections > kMaxSec) return fail(HGA_ERR_INVALID, "n_sections %d outside [1, %d]", n_sections, kMaxSec);
+  if (T < 0 || C < 1 || ldx < C || ldy < C) return fail(HGA_ERR_INVALID, "bad shape");
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  Cascade q;
+  int rc = build_cascade(q, sos, n_sections, nullptr, nullptr, 0, nullptr);
+  if (rc) return rc;
+  if (T == 0) return HGA_OK;
+  const int cg = (C + 31) / 32;
+  k_iir_seq<kExact><<<(cg + 3) / 4, 128, 0, (cudaStream_t)stream>>>(q, x_dev, ldx, y_dev, ldy, nullptr, Segment{0, T, 0}, 1, C, state_dev,
+                                                                    state_dev);
+  LAUNCHED();
+  return HGA_OK;
+}
+
+extern "C" int hga_log_power(int32_t device, const double* data_dev, int64_t rows, int64_t zero_rows, int32_t C, int64_t ld,
+                             int64_t n_frames, int32_t frame_len, int32_t hop, const int64_t* start_dev, const int64_t* stop_dev,
+                             double eps, const double* mu_dev, const double* sigma_dev, double* out_dev, int64_t ldo, void* stream) {
+  if (!out_dev || (!data_dev && rows > 0)) return fail(HGA_ERR_INVALID, "null argument");
+  if ((start_dev == nullptr) != (stop_dev == nullptr)) return fail(HGA_ERR_INVALID, "start and stop must both be given or both be NULL");
+  if ((mu_dev == nullptr) != (sigma_dev == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
+  if (C < 1 || ld < C || ldo < C || rows < 0 || zero_rows < 0) return fail(HGA_ERR_INVALID, "bad shape");
+  if (!start_dev) {
+    if (frame_len < 1 || hop < 1) return fail(HGA_ERR_INVALID, "bad window geometry");
+    const int64_t tot = rows + zero_rows;
+    const int64_t F = tot >= frame_len ? (tot - frame_len) / hop + 1 : 0;
+    if (n_frames > F) return fail(HGA_ERR_INVALID, "n_frames %lld > %lld available", (long long)n_frames, (long long)F);
+  }
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  if (n_frames <= 0) return HGA_OK;
+  dim3 g((unsigned)((C + 31) / 32), (unsigned)((n_frames + 7) / 8), 1);
+  if (g.y > 65535u * 64u) return fail(HGA_ERR_UNSUPPORTED, "too many frames in one call");
+  // grid.y is limited to 65535: fold the excess into several launches
+  const int64_t per = 65535LL * 8;
+  for (int64_t w0 = 0; w0 < n_frames; w0 += per) {
+    const int64_t nf = std::min(per, n_frames - w0);
+    dim3 gg(g.x, (unsigned)((nf + 7) / 8), 1);
+    // window w0+w: shift the data origin for regular windows, the index arrays for irregular ones
+    if (!start_dev) {
+      const int64_t shift = w0 * hop;  // logical rows to skip
+      const int64_t zr = std::max<int64_t>(0, zero_rows - shift), skip = std::max<int64_t>(0, shift - zero_rows);
+      k_frames_seq<<<gg, 256, 0, (cudaStream_t)stream>>>(data_dev + skip * ld, ld, zr, nullptr, Segment{0, rows - skip, w0}, 1, C, nf,
+                                                         frame_len, hop, nullptr, nullptr, eps, mu_dev, sigma_dev, out_dev, ldo);
+    } else {
+      k_frames_seq<<<gg, 256, 0, (cudaStream_t)stream>>>(data_dev, ld, zero_rows, nullptr, Segment{0, rows, w0}, 1, C, nf, frame_len, hop,
+                                                         start_dev + w0, stop_dev + w0, eps, mu_dev, sigma_dev, out_dev, ldo);
+    }
+    LAUNCHED();
+  }
+  return HGA_OK;
+}
+
+extern "C" int hga_zscore(int32_t device, const double* f_dev, int64_t F, int32_t C, int64_t ld, const double* mu_dev,
+                          const double* sigma_dev, double* out_dev, int64_t ldo, void* stream) {
+  if (!f_dev || !mu_dev || !sigma_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (C < 1 || ld < C || ldo < C || F < 0) return fail(HGA_ERR_INVALID, "bad shape");
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  if (F == 0) return HGA_OK;
+  const int64_t n = F * C;
+  k_zscore<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(f_dev, F, C, ld, mu_dev, sigma_dev, out_dev, ldo);
+  LAUNCHED();
+  return HGA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ statistics
+extern "C" int hga_stats_accumulate(int32_t device, const double* feats_dev, int64_t F, int32_t C, int64_t ld, double* acc_dev,
+                                    void* stream) {
+  if (!feats_dev || !acc_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (C < 1 || ld < C || F < 0) return fail(HGA_ERR_INVALID, "bad shape");
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  if (F == 0) return HGA_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int n_sm = 148;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+  const int cg = (C + 31) / 32;
+  int64_t nby = std::max<int64_t>(1, std::min<int64_t>((int64_t)n_sm * 8 / cg, (F + 63) / 64));
+  nby = std::min<int64_t>(nby, 65535);
+  const int64_t rpb = (F + nby - 1) / nby;
+  nby = (F + rpb - 1) / rpb;
+  double* part = nullptr;
+  CU(cudaMallocAsync((void**)&part, (size_t)nby * 3 * C * 8, st));
+  k_stats_partial<<<dim3((unsigned)cg, (unsigned)nby), 256, 0, st>>>(feats_dev, F, C, ld, rpb, part);
+  LAUNCHED();
+  k_stats_merge<<<(C + 127) / 128, 128, 0, st>>>(acc_dev, part, (int)nby, C);
+  LAUNCHED();
+  CU(cudaFreeAsync(part, st));
+  return HGA_OK;
+}
+extern "C" int hga_stats_merge(int32_t device, double* acc_a_dev, const double* acc_b_dev, int32_t count, int32_t C, void* stream) {
+  if (!acc_a_dev || !acc_b_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (C < 1 || count < 0) return fail(HGA_ERR_INVALID, "bad shape");
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  if (count == 0) return HGA_OK;
+  k_stats_merge<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(acc_a_dev, acc_b_dev, count, C);
+  LAUNCHED();
+  return HGA_OK;
+}
+extern "C" int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t C, double* mu_dev, double* sigma_dev, void* stream) {
+  if (!acc_dev || !mu_dev || !sigma_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (C < 1) return fail(HGA_ERR_INVALID, "bad shape");
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  k_stats_finalize<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(acc_dev, C, mu_dev, sigma_dev);
+  LAUNCHED();
+  return HGA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ offline, host buffers
+// Upload x in time slabs on the copy stream; after each slab, launch the work items whose rows are resident; download
+// each group's frame rows on the handle's own stream while the next slab uploads.
+extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
+                                        const int64_t* seg_len, const int64_t* out_row, const double* mu_host, const double* sigma_host,
+                                        double* out_host, int64_t ldo) {
+  if (!h || !x_host || !out_host || !seg_start || !seg_len || !out_row) return fail(HGA_ERR_INVALID, "null argument");
+  const int C = h->cfg.n_channels, L = h->cfg.frame_len, hop = h->cfg.hop;
+  if (ldx < C || ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  if (n_segments < 1) return HGA_OK;
+  CU(cudaSetDevice(h->cfg.device));
+  int rc;
+  int64_t lo = INT64_MAX, hi = 0, olo = INT64_MAX, ohi = 0;
+  for (int i = 0; i < n_segments; ++i) {
+    if (seg_len[i] < L) return fail(HGA_ERR_INVALID, "segment %d has %lld rows < frame_len %d", i, (long long)seg_len[i], L);
+    lo = std::min(lo, seg_start[i]);
+    hi = std::max(hi, seg_start[i] + seg_len[i]);
+    olo = std::min(olo, out_row[i]);
+    ohi = std::max(ohi, out_row[i] + (seg_len[i] - L) / hop + 1);
+  }
+  const size_t row_bytes = (size_t)C * 8;
+  if ((rc = h->xdev.reserve((size_t)(hi - lo) * row_bytes)) || (rc = h->outdev.reserve((size_t)(ohi - olo) * row_bytes))) return rc;
+  cudaStream_t sc = h->s_copy, sk = h->s_own;
+  const double *mu_d, *sig_d;
+  if ((rc = sync_musigma(h, mu_host, sigma_host, sk, &mu_d, &sig_d))) return rc;
+  double* xd = h->xdev.as<double>() - lo * C;     // device row r <-> host row r
+  double* od = h->outdev.as<double>() - olo * C;  // device out row r <-> host out row r
+  const bool fused = h->cfg.precision == HGA_PREC_F64 && h->nb > 0;
+
+  if (!fused) {
+    CU(cudaMemcpy2DAsync(xd + lo * C, row_bytes, x_host + lo * ldx, (size_t)ldx * 8, row_bytes, (size_t)(hi - lo), cudaMemcpyHostToDevice, sk));
+    if ((rc = extract_offline_dev(h, xd, C, n_segments, seg_start, seg_len, out_row, mu_d, sig_d, od, C, sk, nullptr, nullptr))) return rc;
+    CU(cudaMemcpy2DAsync(out_host + olo * ldo, (size_t)ldo * 8, od + olo * C, row_bytes, row_bytes, (size_t)(ohi - olo), cudaMemcpyDeviceToHost, sk));
+    CU(cudaStreamSynchronize(sk));
+    return HGA_OK;
+  }
+  // plan once for the whole table (extract_offline_dev would do the same; here we launch sub-ranges of the work list)
+  {
+    std::vector<int64_t> key;
+    key.insert(key.end(), seg_start, seg_start + n_segments);
+    key.insert(key.end(), seg_len, seg_len + n_segments);
+    key.insert(key.end(), out_row, out_row + n_segments);
+    const int variant = choose_variant(h, n_segments, seg_len);
+    if (key != h->plan_key || variant != h->plan_variant) {
+      const int cg = (C + 31) / 32;
+      const int64_t slots = variant == 1 ? pipe_item_slots(h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
+      plan_chunks(h, n_segments, seg_start, seg_len, out_row, slots, true);
+      if ((rc = upload_plan(h, sk))) return rc;
+      h->plan_key = key;
+      h->plan_variant = variant;
+    }
+  }
+  const int variant = h->plan_variant;
+  const std::vector<Work>& W = h->work_host;
+  const int64_t total_bytes = (hi - lo) * (int64_t)row_bytes;
+  int64_t slab_bytes = std::min<int64_t>(std::max<int64_t>(total_bytes / 12, 16LL << 20), 512LL << 20);
+  const int64_t slab_rows = std::max<int64_t>(hop, slab_bytes / (int64_t)row_bytes / hop * hop);
+  const size_t n_slabs = (size_t)((hi - lo + slab_rows - 1) / slab_rows);
+  while (h->slab_ev.size() < 2 * n_slabs + 2) {
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    h->slab_ev.push_back(e);
+  }
+  size_t next = 0, ev = 0;
+  for (int64_t r0 = lo; r0 < hi; r0 += slab_rows) {
+    const int64_t r1 = std::min(hi, r0 + slab_rows);
+    CU(cudaMemcpy2DAsync(xd + r0 * C, row_bytes, x_host + r0 * ldx, (size_t)ldx * 8, row_bytes, (size_t)(r1 - r0), cudaMemcpyHostToDevice, sc));
+    size_t end = next;
+    while (end < W.size() && W[end].row0 + W[end].t_end <= r1 && W[end].row0 + W[end].t_begin >= lo) ++end;
+    if (r1 == hi) end = W.size();
+    if (end == next) continue;
+    cudaEvent_t e_up = h->slab_ev[ev++];
+    CU(cudaEventRecord(e_up, sc));
+    CU(cudaStreamWaitEvent(sk, e_up, 0));
+    FusedArgs a{xd, C, h->work.as<Work>() + next, (int)(end - next), C, L, hop, h->nb, h->cfg.eps, mu_d, sig_d, od, C, nullptr, nullptr, nullptr, nullptr};
+    if (variant == 1) { if ((rc = launch_pipe(h->q, a, h->n_sm, sk))) return rc; LAUNCHED(); }
+    else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, sk);
+    else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, sk);
+    else rc = launch_fused_seq<kFused>(h, a, sk);
+    if (rc) return rc;
+    // frame rows this group produced
+    int64_t f0 = INT64_MAX, f1 = 0;
+    for (size_t i = next; i < end; ++i) {
+      const Work& w = W[i];
+      const int64_t a0 = w.out_row0 + w.t_acc / hop;                          // first frame: block t_acc/hop + nb-1 -> w = t_acc/hop
+      const int64_t a1 = w.out_row0 + std::max<int64_t>(0, w.t_end / hop - (h->nb - 1));  // one past the last
+      f0 = std::min(f0, a0);
+      f1 = std::max(f1, a1);
+    }
+    if (f1 > f0)
+      CU(cudaMemcpy2DAsync(out_host + f0 * ldo, (size_t)ldo * 8, od + f0 * C, row_bytes, row_bytes, (size_t)(f1 - f0), cudaMemcpyDeviceToHost, sk));
+    next = end;
+  }
+  CU(cudaStreamSynchronize(sk));
+  CU(cudaStreamSynchronize(sc));
+  return HGA_OK;
+}

@@ -1,0 +1,221 @@
+// hga_kernels_exact.cuh — reference-order ("exact") kernels: sequential IIR cascade, row-order window sums, z-score,
+// the single-launch streaming push, and the Chan-merge baseline statistics.
+#pragma once
+#include "hga_common.cuh"
+
+namespace hga {
+
+struct Segment {       // one independent stream (trial / session): rows [row0, row0 + T) of x
+  int64_t row0, T, out_row0;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// K-iir (exact): thread per (segment, channel), sequential in time.  scipy.signal.sosfilt x2 (units.py:151-152).
+// state_in == nullptr: every segment starts from sosfilt_zi (fresh extractor).  state layout (ns, 2, C).
+// ---------------------------------------------------------------------------------------------------------------
+template <int ARITH>
+__global__ void __launch_bounds__(128) k_iir_seq(const __grid_constant__ Cascade q, const double* __restrict__ x,
+                                                 int64_t ldx, double* __restrict__ y, int64_t ldy,
+                                                 const Segment* __restrict__ segs, Segment one, int n_segs, int C,
+                                                 const double* __restrict__ state_in, double* __restrict__ state_out) {
+  const int cg = (C + 31) / 32;
+  const int warp = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  if (warp >= n_segs * cg) return;
+  const int seg = warp / cg, c = (warp % cg) * 32 + (threadIdx.x & 31);
+  if (c >= C) return;
+  const Segment sg = segs ? segs[seg] : one;
+  double z0[kMaxSec], z1[kMaxSec];
+#pragma unroll
+  for (int s = 0; s < kMaxSec; ++s) {
+    z0[s] = state_in ? (s < q.ns ? state_in[(int64_t)(2 * s) * C + c] : 0.0) : q.zi0[s];
+    z1[s] = state_in ? (s < q.ns ? state_in[(int64_t)(2 * s + 1) * C + c] : 0.0) : q.zi1[s];
+  }
+  const double* xp = x + sg.row0 * ldx + c;
+  double* yp = y + sg.row0 * ldy + c;
+  constexpr int U = 8;
+  int64_t t = 0;
+  for (; t + U <= sg.T; t += U) {
+    double v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = __ldg(xp + (t + u) * ldx);
+#pragma unroll
+    for (int u = 0; u < U; ++u) yp[(t + u) * ldy] = cascade<ARITH, 0, kMaxSec>(q, v[u], z0, z1);
+  }
+  for (; t < sg.T; ++t) yp[t * ldy] = cascade<ARITH, 0, kMaxSec>(q, __ldg(xp + t * ldx), z0, z1);
+  if (state_out) {
+#pragma unroll
+    for (int s = 0; s < kMaxSec; ++s)
+      if (s < q.ns) {
+        state_out[(int64_t)(2 * s) * C + c] = z0[s];
+        state_out[(int64_t)(2 * s + 1) * C + c] = z1[s];
+      }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K-frame (exact): compute_log_power_features (hga_optimized.pyx:8-47) + optional z-score (common.py:375-376).
+// Thread per (window, channel); the window's squares are added in row order, unfused, like the reference loop.
+// Rows [0, zero_rows) of the logical matrix are zeros (warm-start padding, pyx:111-122); row r >= zero_rows is
+// data[(r - zero_rows) * ld + c].  Per-segment batching: window w of segment s reads rows relative to seg.row0.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_frames_seq(const double* __restrict__ data, int64_t ld, int64_t zero_rows,
+                                                    const Segment* __restrict__ segs, Segment one, int n_segs, int C,
+                                                    int64_t frames_per_seg_max, int L, int hop,
+                                                    const int64_t* __restrict__ start, const int64_t* __restrict__ stop,
+                                                    double eps, const double* __restrict__ mu,
+                                                    const double* __restrict__ sigma, double* __restrict__ out,
+                                                    int64_t ldo) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int64_t w = (int64_t)blockIdx.y * (blockDim.x / 32) + threadIdx.x / 32;
+  const int seg = blockIdx.z;
+  if (c >= C || seg >= n_segs || w >= frames_per_seg_max) return;
+  const Segment sg = segs ? segs[seg] : one;
+  // frames of this segment: explicit arrays give the count through frames_per_seg_max (single segment only)
+  int64_t a, b;
+  if (start) {
+    a = start[w];
+    b = stop[w];
+  } else {
+    const int64_t rows = sg.T + zero_rows;
+    if (rows < L || w > (rows - L) / hop) return;
+    a = w * hop;
+    b = a + L;
+  }
+  const double* dp = data + sg.row0 * ld + c;
+  double acc = 0.0;
+  for (int64_t r = a; r < b; ++r) {
+    const double v = r < zero_rows ? 0.0 : dp[(r - zero_rows) * ld];
+    acc = __dadd_rn(acc, __dmul_rn(v, v));
+  }
+  const bool zs = mu != nullptr;
+  out[(sg.out_row0 + w) * ldo + c] = feature(acc, (double)(b - a), eps, zs, zs ? mu[c] : 0.0, zs ? sigma[c] : 1.0);
+}
+
+__global__ void k_zscore(const double* __restrict__ f, int64_t F, int C, int64_t ld, const double* __restrict__ mu,
+                         const double* __restrict__ sigma, double* __restrict__ out, int64_t ldo) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F * C) return;
+  const int64_t r = i / C;
+  const int c = (int)(i % C);
+  out[r * ldo + c] = __ddiv_rn(__dsub_rn(f[r * ld + c], mu[c]), sigma[c]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K-stream: one launch per push = sosfilt x2 with carried state (units.py:151-152) + WarmStartFrameBuffer.insert
+// (pyx:96-131) + compute_log_power_features (pyx:27-47) + optional z-score.  Thread per channel; every thread owns
+// its channel's column of the frame buffer `buf` (cap_rows x C), so no inter-thread synchronisation is needed.
+//   y_row0     : row of buf where the new filtered rows go (case 1: 0, case 2: L - n, case 3: overlap)
+//   zero_rows  : rows [0, zero_rows) of buf are zero-filled first (case 2)
+//   rows_total : rows of the logical buffer the windows run over
+// After the frames, the last `overlap` rows are moved to the front (remainder, pyx:106,121,130).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) k_stream_push(const __grid_constant__ Cascade q, const double* __restrict__ x,
+                                                    int64_t ldx, int n, int C, double* __restrict__ state,
+                                                    double* __restrict__ buf, int y_row0, int zero_rows,
+                                                    int rows_total, int overlap, int n_frames, int L, int hop,
+                                                    double eps, const double* __restrict__ mu,
+                                                    const double* __restrict__ sigma, double* __restrict__ out,
+                                                    int64_t ldo) {
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  if (c >= C) return;
+  double z0[kMaxSec], z1[kMaxSec];
+#pragma unroll
+  for (int s = 0; s < kMaxSec; ++s) {
+    z0[s] = s < q.ns ? state[(int64_t)(2 * s) * C + c] : 0.0;
+    z1[s] = s < q.ns ? state[(int64_t)(2 * s + 1) * C + c] : 0.0;
+  }
+  double* bp = buf + c;
+  for (int r = 0; r < zero_rows; ++r) bp[(int64_t)r * C] = 0.0;
+  const double* xp = x + c;
+  for (int t = 0; t < n; ++t)
+    bp[(int64_t)(y_row0 + t) * C] = cascade<kExact, 0, kMaxSec>(q, xp[(int64_t)t * ldx], z0, z1);
+#pragma unroll
+  for (int s = 0; s < kMaxSec; ++s)
+    if (s < q.ns) {
+      state[(int64_t)(2 * s) * C + c] = z0[s];
+      state[(int64_t)(2 * s + 1) * C + c] = z1[s];
+    }
+  const bool zs = mu != nullptr;
+  const double m = zs ? mu[c] : 0.0, sd = zs ? sigma[c] : 1.0;
+  for (int w = 0; w < n_frames; ++w) {
+    double acc = 0.0;
+    const int a = w * hop;
+    for (int r = a; r < a + L; ++r) {
+      const double v = bp[(int64_t)r * C];
+      acc = __dadd_rn(acc, __dmul_rn(v, v));
+    }
+    out[(int64_t)w * ldo + c] = feature(acc, (double)L, eps, zs, m, sd);
+  }
+  const int src = rows_total - overlap;
+  if (src > 0)
+    for (int r = 0; r < overlap; ++r) bp[(int64_t)r * C] = bp[(int64_t)(src + r) * C];  // src > dst: forward is safe
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K-stats: per-channel (n, mean, M2) of F feature rows (np.mean / np.std over frames, prepare_corpus.py:198-199).
+// Each thread reduces a strided set of rows with shifted sums (shift = its first value), partials are Chan-merged in
+// a fixed order: 8 row-lanes per block through shared memory, then blocks by k_stats_merge.  acc layout (3, C).
+// ---------------------------------------------------------------------------------------------------------------
+struct Moments {
+  double n, mean, m2;
+};
+__device__ __forceinline__ Moments chan_merge(Moments a, Moments b) {
+  const double n = a.n + b.n;
+  if (n == 0.0) return a;
+  const double w = b.n / n, d = b.mean - a.mean;
+  return Moments{n, fma(d, w, a.mean), a.m2 + b.m2 + d * d * a.n * w};
+}
+
+constexpr int kStatsRowsPerBlock = 8;
+__global__ void __launch_bounds__(256) k_stats_partial(const double* __restrict__ f, int64_t F, int C, int64_t ld,
+                                                       int64_t rows_per_block, double* __restrict__ part) {
+  __shared__ Moments sm[kStatsRowsPerBlock][33];
+  const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
+  const int64_t r1 = min(F, r0 + rows_per_block);
+  Moments m{0.0, 0.0, 0.0};
+  if (c < C && r0 + ty < r1) {
+    const double k = f[(r0 + ty) * ld + c];
+    double s1 = 0.0, s2 = 0.0, cnt = 0.0;
+    for (int64_t r = r0 + ty; r < r1; r += kStatsRowsPerBlock) {
+      const double d = f[r * ld + c] - k;
+      s1 += d;
+      s2 = fma(d, d, s2);
+      cnt += 1.0;
+    }
+    m = Moments{cnt, k + s1 / cnt, s2 - s1 * s1 / cnt};
+  }
+  sm[ty][lane] = m;
+  __syncthreads();
+  if (ty == 0 && c < C) {
+    Moments a = sm[0][lane];
+    for (int j = 1; j < kStatsRowsPerBlock; ++j) a = chan_merge(a, sm[j][lane]);
+    double* p = part + (int64_t)blockIdx.y * 3 * C;
+    p[c] = a.n;
+    p[C + c] = a.mean;
+    p[2 * C + c] = a.m2;
+  }
+}
+// acc <- merge(acc, part[0], part[1], ..., part[count-1]) in that order (deterministic).
+__global__ void k_stats_merge(double* __restrict__ acc, const double* __restrict__ part, int count, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  Moments a{acc[c], acc[C + c], acc[2 * C + c]};
+  for (int j = 0; j < count; ++j) {
+    const double* p = part + (int64_t)j * 3 * C;
+    a = chan_merge(a, Moments{p[c], p[C + c], p[2 * C + c]});
+  }
+  acc[c] = a.n;
+  acc[C + c] = a.mean;
+  acc[2 * C + c] = a.m2;
+}
+__global__ void k_stats_finalize(const double* __restrict__ acc, int C, double* __restrict__ mu,
+                                 double* __restrict__ sigma) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  mu[c] = acc[C + c];
+  sigma[c] = sqrt(acc[2 * C + c] / acc[c]);
+}
+
+}  // namespace hga

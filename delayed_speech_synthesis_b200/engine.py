@@ -1,0 +1,226 @@
+"""`HgaEngine`: one libhga_b200 handle = one extractor's device state, plus the handle-less building blocks.
+
+Host arrays are numpy float64; device arrays are torch CUDA float64 tensors (torch is plumbing: device memory and
+streams).  Every method ends in a call through the C ABI (include/hga_b200.h); nothing here computes features on the
+CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib, filters
+from ._lib import Config, HgaError, check
+
+
+def _torch():
+    import torch
+
+    return torch
+
+
+def _stream_ptr(device: int) -> int:
+    return int(_torch().cuda.current_stream(device).cuda_stream)
+
+
+def _vec_i64(a: Sequence[int]):
+    arr = np.ascontiguousarray(a, dtype=np.int64)
+    return arr, arr.ctypes.data_as(C.POINTER(C.c_int64))
+
+
+def _host_f64(a, what: str) -> np.ndarray:
+    a = np.asarray(a)
+    if a.dtype != np.float64:
+        raise ValueError(f"{what}: Buffer dtype mismatch, expected 'double' but got '{a.dtype}'")
+    if a.ndim != 2:
+        raise ValueError(f"{what}: Buffer has wrong number of dimensions (expected 2, got {a.ndim})")
+    if a.strides[1] != 8 or a.strides[0] < a.shape[1] * 8 or a.strides[0] % 8:
+        a = np.ascontiguousarray(a)
+    return a
+
+
+def _musigma_host(mu, sigma, n_channels: int) -> Tuple[Optional[np.ndarray], Optional[np.ndarray]]:
+    if mu is None and sigma is None:
+        return None, None
+    if mu is None or sigma is None:
+        raise ValueError("mu and sigma must be given together")
+    mu = np.ascontiguousarray(np.broadcast_to(np.asarray(mu, dtype=np.float64).reshape(-1), (n_channels,)))
+    sigma = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma, dtype=np.float64).reshape(-1), (n_channels,)))
+    return mu, sigma
+
+
+class HgaEngine:
+    """Device-side state of one `HighGammaExtractor` (reference: local/units.py:97-161)."""
+
+    def __init__(self, fs: int, n_channels: int, window_length: float = 0.05, window_shift: float = 0.01,
+                 l_freq: float = 70, h_freq: float = 170, precision: str = "f64", device: Optional[int] = None,
+                 warmup: int = 0, warmup_tol: float = 0.0, max_push_rows: int = 0,
+                 sos_bp: Optional[np.ndarray] = None, sos_notch: Optional[np.ndarray] = None):
+        self._h = None
+        lib = _lib.load()
+        _lib.require_device()
+        if device is None:
+            device = _torch().cuda.current_device()
+        self.device = int(device)
+        self.fs, self.n_channels = int(fs), int(n_channels)
+        self.window_length, self.window_shift = window_length, window_shift
+        self.frame_len, self.hop = filters.window_geometry(fs, window_length, window_shift)
+        if sos_bp is None:
+            sos_bp, sos_notch = filters.design_hga_filters(fs, l_freq, h_freq)
+        self.sos_bp = np.ascontiguousarray(sos_bp, dtype=np.float64)
+        self.sos_notch = np.zeros((0, 6)) if sos_notch is None else np.ascontiguousarray(sos_notch, dtype=np.float64)
+        self.zi_bp = filters.initial_state(self.sos_bp)
+        self.zi_notch = filters.initial_state(self.sos_notch) if len(self.sos_notch) else np.zeros((0, 2))
+        cfg = Config()
+        cfg.abi_version, cfg.device, cfg.fs, cfg.n_channels = _lib.HGA_ABI_VERSION, self.device, self.fs, self.n_channels
+        cfg.frame_len, cfg.hop, cfg.eps = self.frame_len, self.hop, 0.01
+        cfg.n_sections_bp, cfg.n_sections_notch = len(self.sos_bp), len(self.sos_notch)
+        for dst, src in ((cfg.sos_bp, self.sos_bp), (cfg.sos_notch, self.sos_notch), (cfg.zi_bp, self.zi_bp),
+                         (cfg.zi_notch, self.zi_notch)):
+            flat = np.asarray(src, dtype=np.float64).ravel()
+            if len(flat) > len(dst):
+                raise ValueError("too many filter sections")
+            for i, v in enumerate(flat):
+                dst[i] = float(v)
+        cfg.precision = _lib.PRECISIONS[precision]
+        cfg.warmup, cfg.warmup_tol, cfg.max_push_rows = int(warmup), float(warmup_tol), int(max_push_rows)
+        self.precision = precision
+        h = C.c_void_p()
+        check(lib.hga_create(C.byref(cfg), C.byref(h)))
+        self._h, self._lib = h, lib
+        self.warmup = int(lib.hga_warmup(h))
+
+    # -- life cycle ------------------------------------------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.hga_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self) -> None:
+        check(self._lib.hga_reset(self._h, _stream_ptr(self.device)))
+
+    def num_frames(self, rows: int) -> int:
+        return int(self._lib.hga_num_frames(self._h, int(rows)))
+
+    def stream_frames(self, n: int) -> int:
+        return int(self._lib.hga_stream_frames(self._h, int(n)))
+
+    def set_timing(self, on: bool) -> None:
+        check(self._lib.hga_set_timing(self._h, int(on)))
+
+    def last_kernel_ms(self) -> float:
+        return float(self._lib.hga_last_kernel_ms(self._h))
+
+    # -- offline ---------------------------------------------------------------------------------------------------
+    def _segments(self, rows: int, segments):
+        if segments is None:
+            segments = [(0, rows)]
+        start = [int(a) for a, _ in segments]
+        length = [int(b) - int(a) for a, b in segments]
+        frames = [self.num_frames(n) for n in length]
+        out_row = np.concatenate([[0], np.cumsum(frames)])[:-1] if frames else []
+        return start, length, frames, [int(v) for v in out_row]
+
+    def extract_offline(self, x, segments=None, mu=None, sigma=None, out=None):
+        """Features of independent segments [(start, stop), ...] of x, each from a fresh extractor, concatenated
+        (prepare_corpus.py:42-52) with the optional offline z-score (prepare_corpus.py:226-227).
+
+        x: torch CUDA float64 (T, C) -> returns a torch CUDA tensor (enqueued on the current stream);
+        x: numpy float64 (T, C)      -> returns numpy (pipelined host<->device copies inside the call)."""
+        torch = _torch()
+        if isinstance(x, torch.Tensor):
+            if not x.is_cuda or x.dtype != torch.float64 or x.dim() != 2 or x.stride(1) != 1:
+                raise ValueError("device input must be a CUDA float64 (T, C) tensor with unit channel stride")
+            start, length, frames, out_row = self._segments(x.shape[0], segments)
+            total = int(sum(frames))
+            if out is None:
+                out = torch.empty((total, self.n_channels), dtype=torch.float64, device=x.device)
+            mu_t = sg_t = None
+            if mu is not None:
+                mu_t = torch.as_tensor(mu, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
+                sg_t = torch.as_tensor(sigma, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
+            (_, ps), (_, pl), (_, po) = a1, a2, a3 = _vec_i64(start), _vec_i64(length), _vec_i64(out_row)
+            check(self._lib.hga_extract_offline(self._h, x.data_ptr(), x.stride(0), len(start), ps, pl, po,
+                                                mu_t.data_ptr() if mu_t is not None else None,
+                                                sg_t.data_ptr() if sg_t is not None else None,
+                                                out.data_ptr(), out.stride(0), _stream_ptr(self.device)))
+            return out
+        x = _host_f64(x, "data")
+        start, length, frames, out_row = self._segments(x.shape[0], segments)
+        total = int(sum(frames))
+        if out is None:
+            out = np.empty((total, self.n_channels), dtype=np.float64)
+        mu_h, sg_h = _musigma_host(mu, sigma, self.n_channels)
+        (_, ps), (_, pl), (_, po) = a1, a2, a3 = _vec_i64(start), _vec_i64(length), _vec_i64(out_row)
+        check(self._lib.hga_extract_offline_host(self._h, x.ctypes.data, x.strides[0] // 8, len(start), ps, pl, po,
+                                                 mu_h.ctypes.data if mu_h is not None else None,
+                                                 sg_h.ctypes.data if sg_h is not None else None,
+                                                 out.ctypes.data, out.strides[0] // 8))
+        return out
+
+    # -- streaming -------------------------------------------------------------------------------------------------
+    def push(self, x, mu=None, sigma=None):
+        """`extract_features` of the long-lived extractor on the next n rows (local/units.py:151-160)."""
+        torch = _torch()
+        nf = C.c_int64(0)
+        if isinstance(x, torch.Tensor):
+            if not x.is_cuda or x.dtype != torch.float64 or x.dim() != 2 or x.stride(1) != 1:
+                raise ValueError("device input must be a CUDA float64 (n, C) tensor with unit channel stride")
+            frames = self.stream_frames(x.shape[0])
+            out = torch.empty((frames, self.n_channels), dtype=torch.float64, device=x.device)
+            mu_t = sg_t = None
+            if mu is not None:
+                mu_t = torch.as_tensor(mu, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
+                sg_t = torch.as_tensor(sigma, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
+            check(self._lib.hga_stream_push(self._h, x.data_ptr(), x.shape[0], x.stride(0),
+                                            mu_t.data_ptr() if mu_t is not None else None,
+                                            sg_t.data_ptr() if sg_t is not None else None,
+                                            out.data_ptr(), max(out.stride(0), self.n_channels), C.byref(nf),
+                                            _stream_ptr(self.device)))
+            return out
+        x = _host_f64(x, "data")
+        if x.shape[1] != self.n_channels:
+            raise ValueError(f"expected {self.n_channels} channels, got {x.shape[1]}")
+        frames = self.stream_frames(x.shape[0])
+        out = np.empty((frames, self.n_channels), dtype=np.float64)
+        mu_h, sg_h = _musigma_host(mu, sigma, self.n_channels)
+        check(self._lib.hga_stream_push_host(self._h, x.ctypes.data, x.shape[0], x.strides[0] // 8,
+                                             mu_h.ctypes.data if mu_h is not None else None,
+                                             sg_h.ctypes.data if sg_h is not None else None,
+                                             out.ctypes.data, self.n_channels, C.byref(nf)))
+        assert nf.value == frames
+        return out
+
+    def get_state(self):
+        """(hg_state (S,2,C), fh_state (S,2,C), remainder (L-hop, C), first_frame) in the reference's shapes."""
+        Cn = self.n_channels
+        hg = np.empty((len(self.sos_bp), 2, Cn))
+        fh = np.empty((len(self.sos_notch), 2, Cn))
+        rem = np.empty((self.frame_len - self.hop, Cn))
+        ff = C.c_int32(0)
+        check(self._lib.hga_get_state(self._h, hg.ctypes.data, fh.ctypes.data if fh.size else None,
+                                      rem.ctypes.data if rem.size else None, C.byref(ff)))
+        return hg, fh, rem, bool(ff.value)
+
+    def set_state(self, hg=None, fh=None, remainder=None, first_frame=None) -> None:
+        def prep(a, shape):
+            if a is None:
+                return None, None
+            a = np.ascontiguousarray(a, dtype=np.float64)
+            if a.shape != shape:
+                raise ValueError(f"state shape {a.shape} != {shape}")
+            return a, a.ctypes.data
+        Cn = self.n_channels
+        hg, p1 = prep(hg, (len(self.sos_bp), 2, Cn))
+        fh, p2 = prep(fh, (len(self.sos_notch), 2, Cn))
+        rem, p3 = prep(remainder, (self.frame_len - self.hop, Cn))
+        ff = None if first_frame is None else C.c_int32(int(bool(first_frame)))
+        check(self._lib.hga_set_state(self._h, p1, p2, p3, C.byref(ff) if ff is not None else None))

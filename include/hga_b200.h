@@ -1,0 +1,168 @@
+/* hga_b200.h — C ABI of libhga_b200.so: the B200 (sm_100a) implementation of the high-gamma-activity (HGA) front end
+ * of cronelab/delayed-speech-synthesis.
+ *
+ * The reference has no C ABI for this path; its boundary is a Python call surface.  Every entry point
+ * below names the reference interface it stands behind (paths relative to /root/reference).  The Python package
+ * `delayed_speech_synthesis_b200` binds these with ctypes (see INTEGRATION.md for the stub a maintainer would add to
+ * the reference).
+ *
+ * Conventions
+ *   - plain C types only; every function returns an `int` status (HGA_OK == 0) and never throws;
+ *     `hga_last_error()` returns a thread-local message for the last non-zero status.
+ *   - matrices are float64, row-major, time along rows: x[t * ld + c]  (the reference's (T, C) ndarray layout,
+ *     local/units.py:81,145).
+ *   - pointers named `*_dev` are device pointers on the handle's device; `*_host` are host pointers; `stream` is a
+ *     `cudaStream_t` passed as `void*` (NULL = the legacy default stream).  Device entry points only enqueue work;
+ *     host entry points return after the result is in the caller's buffer.
+ *   - a handle is used by one host thread at a time; distinct handles are independent.
+ */
+#ifndef HGA_B200_H
+#define HGA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HGA_ABI_VERSION 1
+#define HGA_MAX_SECTIONS 8 /* biquads per filter (the reference designs order-8 Butterworth band filters = 8 SOS) */
+
+enum hga_status {
+  HGA_OK = 0,
+  HGA_ERR_INVALID = 1,     /* bad argument */
+  HGA_ERR_CUDA = 2,        /* CUDA runtime error (message has the cudaError string) */
+  HGA_ERR_NO_DEVICE = 3,   /* no CUDA device: there is NO CPU fallback */
+  HGA_ERR_UNSUPPORTED = 4, /* configuration outside what the kernels implement */
+  HGA_ERR_NOMEM = 5
+};
+
+enum hga_precision {
+  /* Unfused IEEE double arithmetic in the reference's operation order, sequential in time per channel, windows summed
+   * in row order: bit-identical to scipy.signal.sosfilt (x2) -> compute_log_power_features up to the final log()
+   * (CUDA log is <= 1 ulp; glibc's is correctly rounded in almost all cases).  Used for streaming and short trials. */
+  HGA_PREC_EXACT = 0,
+  /* float64 with fused multiply-adds, time-chunked (each chunk re-filters `warmup` samples of history from zero
+   * state), window power as the sum of hop-block partial sums.  |feature - reference| <= 1e-9 (tests state it). */
+  HGA_PREC_F64 = 1
+};
+
+/* Configuration of one extractor = the constructor arguments of HighGammaExtractor (local/units.py:102-132) after the
+ * host has designed the filters (local/units.py:124-126) and taken sosfilt_zi (local/units.py:128-129).            */
+typedef struct hga_config {
+  int32_t abi_version;                   /* HGA_ABI_VERSION */
+  int32_t device;                        /* CUDA device ordinal */
+  int32_t fs;                            /* sampling rate, Hz */
+  int32_t n_channels;                    /* nb_electrodes (C) */
+  int32_t frame_len;                     /* L   = int(window_length * fs)   (hga_optimized.pyx:77) */
+  int32_t hop;                           /* hop = int(window_shift  * fs)   (hga_optimized.pyx:76) */
+  double eps;                            /* 0.01 (hga_optimized.pyx:46) */
+  int32_t n_sections_bp;                 /* sections of hg_filter (band-pass 70-170 Hz), <= HGA_MAX_SECTIONS */
+  int32_t n_sections_notch;              /* sections of fh_filter (band-stop 118-122 Hz); 0 = no second filter */
+  double sos_bp[HGA_MAX_SECTIONS * 6];   /* scipy SOS rows [b0 b1 b2 a0 a1 a2], a0 == 1 */
+  double sos_notch[HGA_MAX_SECTIONS * 6];
+  double zi_bp[HGA_MAX_SECTIONS * 2];    /* sosfilt_zi(sos): initial (z0, z1) per section, tiled over channels,
+                                            NOT scaled by x[0] (local/units.py:128-132) */
+  double zi_notch[HGA_MAX_SECTIONS * 2];
+  int32_t precision;                     /* enum hga_precision: arithmetic of hga_extract_offline* */
+  int32_t warmup;                        /* HGA_PREC_F64: history re-filtered per time-chunk; 0 = derive from
+                                            warmup_tol and the largest pole radius */
+  double warmup_tol;                     /* target truncation error of the warm-up (default 1e-10 when 0) */
+  int32_t max_push_rows;                 /* largest n accepted by hga_stream_push (0 = 4096) */
+  int32_t reserved;
+} hga_config;
+
+typedef struct hga_handle hga_handle;
+
+/* ---- life cycle ------------------------------------------------------------------------------------------------ */
+const char* hga_last_error(void);
+int hga_abi_version(void);
+/* Number of CUDA devices visible (0 on a CPU-only box; never fails). */
+int hga_device_count(void);
+
+/* HighGammaExtractor.__init__ (local/units.py:102-132) + WarmStartFrameBuffer.__init__ (hga_optimized.pyx:65-88). */
+int hga_create(const hga_config* cfg, hga_handle** out);
+int hga_destroy(hga_handle* h);
+/* A fresh extractor: zi re-tiled, frame buffer zeroed and re-armed (WarmStartFrameBuffer.reset, pyx:90-94; the
+ * reference gets the same effect by constructing a new extractor per trial, prepare_corpus.py:48). */
+int hga_reset(hga_handle* h, void* stream);
+/* Effective warm-up length (samples) the handle uses in HGA_PREC_F64 mode. */
+int hga_warmup(const hga_handle* h);
+
+/* ---- offline: batched independent segments (prepare_corpus.py:42-52; baseline_offline.py:45-50) ------------------ */
+/* Frames a single call on `rows` filtered rows yields: compute_log_power_features' count (hga_optimized.pyx:36),
+ * evaluated with the reference's C-float arithmetic. */
+int64_t hga_num_frames(const hga_handle* h, int64_t rows);
+
+/* For each segment i (rows [seg_start[i], seg_start[i]+seg_len[i]) of x): fresh extractor -> extract_features ->
+ * optional z-score (prepare_corpus.py:226-227).  seg_len[i] must be >= frame_len (frame-buffer case 1,
+ * pyx:104-107).  Features of segment i are written to out rows [out_row[i], out_row[i]+hga_num_frames(seg_len[i])).
+ * seg_start/seg_len/out_row are HOST arrays.  mu_dev/sigma_dev: (C,) or NULL.  Does not touch the streaming state. */
+int hga_extract_offline(hga_handle* h, const double* x_dev, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
+                        const int64_t* seg_len, const int64_t* out_row, const double* mu_dev, const double* sigma_dev,
+                        double* out_dev, int64_t ldo, void* stream);
+/* Same with HOST buffers (x, mu, sigma, out): stages through pinned memory, overlapping the host<->device copies of
+ * consecutive time slabs with the kernels; returns when `out_host` is complete. */
+int hga_extract_offline_host(hga_handle* h, const double* x_host, int64_t ldx, int32_t n_segments,
+                             const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
+                             const double* mu_host, const double* sigma_host, double* out_host, int64_t ldo);
+
+/* ---- streaming: HighGammaExtractor.extract_features on a long-lived extractor (local/units.py:145-161,203-207) --- */
+/* Frames the next push of n rows will yield given the handle's frame-buffer state (cases 1-3, pyx:96-131). */
+int64_t hga_stream_frames(const hga_handle* h, int64_t n);
+/* Filter n new rows (state carried), run the warm-start frame buffer, emit log-power frames, optional z-score.
+ * x/out/mu/sigma are device pointers.  *n_frames receives the number of rows written to out. */
+int hga_stream_push(hga_handle* h, const double* x_dev, int64_t n, int64_t ldx, const double* mu_dev,
+                    const double* sigma_dev, double* out_dev, int64_t ldo, int64_t* n_frames, void* stream);
+/* Same with HOST buffers; mu/sigma (host, (C,) or NULL) are cached on the device and re-uploaded only when the
+ * pointer's contents change.  One kernel launch per call; returns when out_host holds the frames. */
+int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t n, int64_t ldx, const double* mu_host,
+                         const double* sigma_host, double* out_host, int64_t ldo, int64_t* n_frames);
+
+/* Streaming state, in the reference's own shapes: hg_state/fh_state (n_sections, 2, C) as local/units.py:131-132,
+ * remainder (frame_len - hop, C) and the first_frame flag as hga_optimized.pyx:78-88.  HOST buffers; NULL = skip. */
+int hga_get_state(hga_handle* h, double* hg_state, double* fh_state, double* remainder, int32_t* first_frame);
+int hga_set_state(hga_handle* h, const double* hg_state, const double* fh_state, const double* remainder,
+                  const int32_t* first_frame);
+
+/* ---- building blocks (the extension module's own functions) ---------------------------------------------------- */
+/* scipy.signal.sosfilt(sos, x, axis=0, zi=state) for one filter of n_sections <= 16 (local/units.py:151-152):
+ * y (T, C) and state (n_sections, 2, C) updated in place.  Unfused double arithmetic (bit-identical to scipy). */
+int hga_sosfilt(int32_t device, const double* sos /*host (n_sections,6)*/, int32_t n_sections, const double* x_dev,
+                int64_t T, int32_t C, int64_t ldx, double* state_dev, double* y_dev, int64_t ldy, void* stream);
+/* compute_log_power_features (hga_optimized.pyx:27-47) on a device matrix of `rows` rows preceded by `zero_rows`
+ * virtual rows of zeros: out[w, c] = log(sum_{r in [start_w, stop_w)} data[r, c]^2 / (stop_w - start_w) + eps),
+ * sequential sums.  Regular windows: start_w = w * hop, stop_w = start_w + frame_len (start_dev/stop_dev NULL);
+ * irregular windows: explicit device index arrays (n_frames,).  Optional z-score with mu_dev/sigma_dev. */
+int hga_log_power(int32_t device, const double* data_dev, int64_t rows, int64_t zero_rows, int32_t C, int64_t ld,
+                  int64_t n_frames, int32_t frame_len, int32_t hop, const int64_t* start_dev, const int64_t* stop_dev,
+                  double eps, const double* mu_dev, const double* sigma_dev, double* out_dev, int64_t ldo,
+                  void* stream);
+/* ZScoreNormalization.__call__ (local/common.py:375-376): out = (f - mu) / sigma, in place allowed. */
+int hga_zscore(int32_t device, const double* f_dev, int64_t F, int32_t C, int64_t ld, const double* mu_dev,
+               const double* sigma_dev, double* out_dev, int64_t ldo, void* stream);
+
+/* ---- baseline statistics (prepare_corpus.py:190-199; baseline_offline.py:45-60) --------------------------------- */
+/* acc_dev is (3, C) float64: rows n, mean, M2 (sum of squared deviations).  Zero-initialise to start.
+ * accumulate: Chan-merges the F frames of feats into acc.  merge: acc_a <- merge(acc_a, acc_b) for `count`
+ * consecutive accumulators in acc_b (fixed order: deterministic).  finalize: mu = mean, sigma = sqrt(M2 / n)
+ * (population std, ddof = 0, as np.std). */
+int hga_stats_accumulate(int32_t device, const double* feats_dev, int64_t F, int32_t C, int64_t ld, double* acc_dev,
+                         void* stream);
+int hga_stats_merge(int32_t device, double* acc_a_dev, const double* acc_b_dev, int32_t count, int32_t C,
+                    void* stream);
+int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t C, double* mu_dev, double* sigma_dev,
+                       void* stream);
+
+/* ---- introspection for bench.py / tests ------------------------------------------------------------------------- */
+/* Kernel launches issued through this library by the calling process since load (all handles). */
+int64_t hga_launch_count(void);
+/* Device time (ms, CUDA events on the launching stream) of the dominant kernel of the last hga_extract_offline call
+ * on this handle when timing was enabled with hga_set_timing(h, 1); -1 if unavailable. */
+int hga_set_timing(hga_handle* h, int32_t enable);
+double hga_last_kernel_ms(hga_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HGA_B200_H */

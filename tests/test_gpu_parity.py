@@ -1,0 +1,292 @@
+"""GPU parity: the CUDA path (through the C ABI, via the Python host layer) against the CPU oracle on identical seeded
+inputs.  Tolerances (stated here, per feature = per (frame, channel) element):
+  * 'exact' precision and every streaming push <= 1024 rows: the arithmetic is the reference's, only the final log()
+    may differ by one ulp  ->  max-abs <= 4e-15, max-rel <= 4e-15 on features (|f| < 8).
+  * 'f64' precision (fused multiply-adds, hop-block sums, warm-up truncation 1e-10): max-abs <= 1e-9 on features,
+    <= 5e-9 on z-scores (division by sigma ~ 0.4); relative error <= 1e-8 where |f| > 1e-2.
+  * filtered samples (hga_sosfilt) and filter states: bit-identical to scipy.signal.sosfilt.
+  * baseline mu / sigma: relative error <= 1e-12.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import hga_oracle as O  # noqa: E402  (the checker; never on the product path)
+from oracle import c_oracle as CO  # noqa: E402
+
+TOL_EXACT = 4e-15
+TOL_F64 = 1e-9
+
+
+def _oracle_offline(x, fs, mu=None, sigma=None, segments=None):
+    """Fresh extractor per segment, one call each, offline z-score — via the C restatement (bit-identical to the
+    NumPy oracle, asserted in tests/test_oracle.py)."""
+    bp, nt = O.design_hga_filters(fs)
+    from scipy.signal import sosfilt_zi
+    L, hop = int(0.05 * fs), int(0.01 * fs)
+    segments = [(0, len(x))] if segments is None else segments
+    return np.concatenate([CO.extract_fused(x[a:b], bp, sosfilt_zi(bp), nt, sosfilt_zi(nt), L, hop, mu=mu, sigma=sigma)
+                           for a, b in segments])
+
+
+def _err(a, b):
+    d = np.abs(a - b)
+    return d.max(), (d / np.maximum(np.abs(b), 1e-2)).max()
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    return torch
+
+
+# ------------------------------------------------------------------------------------------------------------ sosfilt
+@pytest.mark.parametrize("which", ["bp", "notch"])
+def test_sosfilt_bit_exact(which):
+    from scipy.signal import sosfilt
+    from delayed_speech_synthesis_b200 import ops
+    fs, T, C = 1000, 3000, 37
+    x = O.synthetic_ecog(T, C, fs, "ecog")
+    sos = O.design_hga_filters(fs)[0 if which == "bp" else 1]
+    zi = O.tiled_zi(sos, C)
+    y_ref, zf_ref = sosfilt(sos, x, axis=0, zi=zi)
+    y, zf = ops.sosfilt(sos, x, zi)
+    assert np.array_equal(y, y_ref)
+    assert np.array_equal(zf, zf_ref)
+
+
+# ---------------------------------------------------------------------------------------------------------- log power
+@pytest.mark.parametrize("rows,C,fs", [(1000, 4, 1000), (50, 1, 1000), (257, 33, 1000), (1000, 8, 2000), (49, 3, 1000)])
+def test_log_power_matches_reference_function(rows, C, fs):
+    from delayed_speech_synthesis_b200.hga_optimized import compute_log_power_features
+    data = O.synthetic_ecog(rows, C, fs, "white", session=3)
+    ref = O.compute_log_power_features(data, fs, 0.05, 0.01)
+    got = compute_log_power_features(data, fs, 0.05, 0.01)
+    assert got.shape == ref.shape and got.dtype == np.float64
+    if ref.size:
+        assert _err(got, ref)[0] <= TOL_EXACT
+
+
+def test_log_power_strided_and_errors():
+    from delayed_speech_synthesis_b200.hga_optimized import compute_log_power_features
+    big = O.synthetic_ecog(400, 12, 1000, "white")
+    view = big[::2, 1:9]                                    # non-contiguous: "any strides accepted"
+    ref = O.compute_log_power_features(np.ascontiguousarray(view), 1000, 0.05, 0.01)
+    assert _err(compute_log_power_features(view, 1000, 0.05, 0.01), ref)[0] <= TOL_EXACT
+    with pytest.raises(ValueError):
+        compute_log_power_features(big.astype(np.float32), 1000, 0.05, 0.01)
+    with pytest.raises(ValueError):
+        compute_log_power_features(big[0], 1000, 0.05, 0.01)
+
+
+def test_log_power_irregular_windows():
+    """window_shift = 0.0125 s at 1 kHz: the reference's float32 index arithmetic rounds starts off any regular grid."""
+    from delayed_speech_synthesis_b200.hga_optimized import compute_log_power_features
+    data = O.synthetic_ecog(700, 5, 1000, "white", session=9)
+    ref = O.compute_log_power_features(data, 1000, 0.05, 0.0125)
+    got = compute_log_power_features(data, 1000, 0.05, 0.0125)
+    assert got.shape == ref.shape
+    assert _err(got, ref)[0] <= TOL_EXACT
+
+
+def test_known_answers():
+    """Constant input -> band-pass output decays to 0 -> feature -> log(0.01); a unit step with the unscaled
+    sosfilt_zi state is the notch filter's exact steady state."""
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    ex = HighGammaExtractor(1000, 4, precision="exact")
+    f = ex.extract_features(np.full((20000, 4), 3.0))
+    assert abs(f[-1] - np.log(0.01)).max() < 1e-9
+
+
+# ------------------------------------------------------------------------------------------------------------ offline
+@pytest.mark.parametrize("precision,tol", [("exact", TOL_EXACT), ("f64", TOL_F64)])
+@pytest.mark.parametrize("kind", ["white", "ecog"])
+def test_offline_k1_shape(precision, tol, kind):
+    """BASELINE config 1: 128 ch x 60 s @ 1 kHz, single call on a fresh extractor."""
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    fs, T, C = 1000, 60000, 128
+    x = O.synthetic_ecog(T, C, fs, kind)
+    ref = _oracle_offline(x, fs)
+    got = HighGammaExtractor(fs, C, precision=precision).extract_features(x)
+    assert got.shape == ref.shape == (5996, C)
+    a, r = _err(got, ref)
+    assert a <= tol and r <= 10 * tol, (a, r)
+
+
+@pytest.mark.parametrize("precision,tol", [("exact", TOL_EXACT), ("f64", TOL_F64)])
+def test_offline_segments_and_zscore(precision, tol):
+    """Trials as in prepare_corpus.py:42-52 (fresh extractor each, ragged lengths incl. the minimum L) + z-score."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, C = 1000, 64
+    x = O.synthetic_ecog(30000, C, fs, "ecog", session=1)
+    segs = [(0, 2540), (2540, 2590), (3000, 9017), (9017, 30000)]
+    base = _oracle_offline(x, fs, segments=segs)
+    mu, sigma = base.mean(0), base.std(0)
+    ref = _oracle_offline(x, fs, mu, sigma, segments=segs)
+    eng = HgaEngine(fs, C, precision=precision)
+    got = eng.extract_offline(x, segs, mu, sigma)
+    assert got.shape == ref.shape
+    a, r = _err(got, ref)
+    assert a <= 5 * tol, (a, r)
+
+
+def test_offline_device_tensor_matches_host(torch):
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, C = 1000, 128
+    x = O.synthetic_ecog(120000, C, fs, "white", session=2)
+    eng = HgaEngine(fs, C, precision="f64")
+    host = eng.extract_offline(x)
+    dev = eng.extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert np.array_equal(host, dev)
+    assert _err(host, _oracle_offline(x, fs))[0] <= TOL_F64
+
+
+def test_offline_time_chunked_long(torch):
+    """10 min x 128 ch: many time-chunks with warm-up; oracle via the multi-threaded C restatement."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, C = 1000, 600000, 128
+    x = O.synthetic_ecog(T, C, fs, "white", session=5)
+    x += 5.0 * np.sin(2 * np.pi * 120 * np.arange(T) / fs)[:, None]   # line harmonic sitting in the notch
+    ref = _oracle_offline(x, fs)
+    got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    a, r = _err(got, ref)
+    assert a <= TOL_F64, (a, r)
+
+
+def test_offline_2khz_high_density_prefix(torch):
+    """BASELINE config 4 geometry (2 kHz: L = 100, hop = 20) on a 1024-channel, 30 s prefix."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, C = 2000, 60000, 1024
+    x = O.synthetic_ecog(T, C, fs, "white", session=6)
+    ref = _oracle_offline(x, fs)
+    got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert got.shape == ref.shape == (2996, C)
+    assert _err(got, ref)[0] <= TOL_F64
+
+
+def test_offline_rejects_short_segment():
+    from delayed_speech_synthesis_b200 import HgaError
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    eng = HgaEngine(1000, 8)
+    with pytest.raises(HgaError):
+        eng.extract_offline(np.zeros((49, 8)))
+
+
+# ---------------------------------------------------------------------------------------------------------- streaming
+@pytest.mark.parametrize("chunks", [[10] * 60, [40] * 20, [20, 10, 10, 40, 70, 10, 30], [60, 10, 10, 25, 13, 50], [7, 9, 33, 10, 10]])
+def test_streaming_matches_oracle_unit(chunks):
+    """Long-lived extractor fed packet by packet (decode_online.py): all three frame-buffer cases, ragged packets that
+    drift off the hop grid, fused z-score.  Arithmetic is reference-order -> ulp-level agreement."""
+    from delayed_speech_synthesis_b200.common import ZScoreNormalization
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    fs, C = 1000, 64
+    x = O.synthetic_ecog(sum(chunks), C, fs, "ecog", session=4)
+    rng = np.random.default_rng(0)
+    mu, sigma = rng.normal(3, 1, (1, C)), rng.uniform(0.3, 0.6, (1, C))
+    ref_ex = O.HighGammaExtractor(fs, C, post_transforms=[O.ZScoreNormalization(mu, sigma)], log_power=O.compute_log_power_features)
+    ex = HighGammaExtractor(fs, C, post_transforms=[ZScoreNormalization(mu, sigma)])
+    t = 0
+    for n in chunks:
+        ref = ref_ex.extract_features(x[t:t + n])
+        got = ex.extract_features(x[t:t + n])
+        assert got.shape == ref.shape, (n, got.shape, ref.shape)
+        if ref.size:
+            assert _err(got, ref)[0] <= 10 * TOL_EXACT
+        t += n
+    assert np.array_equal(ex.hg_state, ref_ex.hg_state)
+    assert np.array_equal(ex.fh_state, ref_ex.fh_state)
+
+
+def test_streaming_equals_offline_with_zero_pad():
+    """SURVEY §8c pin (i): 10-sample pushes == offline framing of [40 zero rows ; filtered signal]."""
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    from delayed_speech_synthesis_b200 import ops
+    fs, C, n = 1000, 16, 10
+    x = O.synthetic_ecog(3000, C, fs, "white", session=8)
+    ex = HighGammaExtractor(fs, C)
+    stream = np.concatenate([ex.extract_features(x[t:t + n]) for t in range(0, len(x), n)])
+    oe = O.HighGammaExtractor(fs, C)
+    y = oe.filtered(x)
+    off = ops.log_power(y, fs, 0.05, 0.01, zero_rows=40)
+    assert stream.shape == off.shape == (300, C)
+    assert np.array_equal(stream, off)
+
+
+@pytest.mark.parametrize("precision,tol", [("exact", TOL_EXACT), ("f64", TOL_F64)])
+def test_bulk_push_carries_state(precision, tol, torch):
+    """Large pushes (bulk path) interleaved with packets: state, remainder and frame grid carry across both paths."""
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    fs, C = 1000, 32
+    chunks = [5000, 10, 10, 30000, 40, 2003, 10]
+    x = O.synthetic_ecog(sum(chunks), C, fs, "ecog", session=7)
+    ref_ex, ex = O.HighGammaExtractor(fs, C), HighGammaExtractor(fs, C, precision=precision)
+    t = 0
+    for n in chunks:
+        ref, got = ref_ex.extract_features(x[t:t + n]), ex.extract_features(x[t:t + n])
+        assert got.shape == ref.shape, (n, got.shape, ref.shape)
+        assert _err(got, ref)[0] <= tol, n
+        t += n
+    np.testing.assert_allclose(ex.fh_state, ref_ex.fh_state, rtol=0, atol=1e-9 if precision == "f64" else 0)
+
+
+def test_state_roundtrip_and_reset():
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    fs, C = 1000, 8
+    x = O.synthetic_ecog(200, C, fs, "white")
+    a, b = HighGammaExtractor(fs, C), HighGammaExtractor(fs, C)
+    for t in range(0, 100, 10):
+        a.extract_features(x[t:t + 10])
+    hg, fh, rem, ff = a._engine.get_state()
+    b._engine.set_state(hg, fh, rem, ff)
+    assert np.array_equal(a.extract_features(x[100:110]), b.extract_features(x[100:110]))
+    assert np.array_equal(HighGammaExtractor(fs, C).hg_state, O.tiled_zi(a.hg_filter, C))
+    a._engine.reset()
+    fresh = HighGammaExtractor(fs, C)
+    assert np.array_equal(a.extract_features(x[:10]), fresh.extract_features(x[:10]))
+
+
+def test_unit_message_interface():
+    import asyncio
+    from delayed_speech_synthesis_b200.ezmsg_compat import TimeSeriesMessage
+    from delayed_speech_synthesis_b200.units import HighGammaActivity, HighGammaActivitySettings
+    unit = HighGammaActivity(HighGammaActivitySettings(fs=1000, nb_electrodes=16))
+    unit.setup()
+    x = O.synthetic_ecog(40, 16, 1000, "white")
+
+    async def run():
+        return [m async for m in unit.process(TimeSeriesMessage(data=x, fs=1000.0))]
+    (stream, msg), = asyncio.run(run())
+    assert stream is unit.OUTPUT and msg.fs == 100.0 and msg.data.shape == (1, 16)
+    ref = O.HighGammaExtractor(1000, 16).extract_features(x)
+    assert _err(msg.data, ref)[0] <= 10 * TOL_EXACT
+
+
+# --------------------------------------------------------------------------------------------------------- statistics
+def test_baseline_statistics_and_merge(torch):
+    from delayed_speech_synthesis_b200.ops import ChannelStats
+    rng = np.random.default_rng(1)
+    trials = [rng.normal(3.0, 0.4, (n, 128)) + np.linspace(-2, 6, 128) for n in (250, 311, 1, 4096, 77)]
+    mu_ref, sd_ref = O.baseline_statistics(trials)
+    st = ChannelStats(128)
+    for t in trials:
+        st.update(t)
+    mu, sd = st.finalize()
+    np.testing.assert_allclose(mu, mu_ref, rtol=1e-12, atol=0)
+    np.testing.assert_allclose(sd, sd_ref, rtol=1e-12, atol=0)
+    # two "ranks": merged accumulators == single accumulator
+    a, b = ChannelStats(128), ChannelStats(128)
+    for t in trials[:2]:
+        a.update(t)
+    for t in trials[2:]:
+        b.update(t)
+    mu2, sd2 = a.merge(b).finalize()
+    np.testing.assert_allclose(mu2, mu_ref, rtol=1e-12, atol=0)
+    np.testing.assert_allclose(sd2, sd_ref, rtol=1e-12, atol=0)
+
+
+def test_zscore_callable_matches_numpy():
+    from delayed_speech_synthesis_b200.common import ZScoreNormalization
+    rng = np.random.default_rng(2)
+    f, mu, sd = rng.normal(size=(500, 64)), rng.normal(size=64), rng.uniform(0.2, 2, 64)
+    assert np.array_equal(ZScoreNormalization(mu, sd)(f), (f - mu) / sd)
