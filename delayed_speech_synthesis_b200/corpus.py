@@ -24,9 +24,9 @@ def gather_accumulators(acc, group=None):
     if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
         return a
     world = dist.get_world_size(group)
-    out = torch.empty((world,) + tuple(a.shape), dtype=a.dtype, device=a.device)
+    out = torch.empty((world * a.shape[0],) + tuple(a.shape[1:]), dtype=a.dtype, device=a.device)
     dist.all_gather_into_tensor(out, a, group=group)
-    return out.reshape(-1, 3, a.shape[-1])
+    return out
 
 
 def day_slots(days: Sequence[int]) -> Dict[int, int]:

@@ -175,7 +175,7 @@ class HgaEngine:
             if not x.is_cuda or x.dtype != torch.float64 or x.dim() != 2 or x.stride(1) != 1:
                 raise ValueError("device input must be a CUDA float64 (n, C) tensor with unit channel stride")
             frames = self.stream_frames(x.shape[0])
-            out = torch.empty((frames, self.n_channels), dtype=torch.float64, device=x.device)
+            out = torch.empty((max(frames, 1), self.n_channels), dtype=torch.float64, device=x.device)[:frames]
             mu_t = sg_t = None
             if mu is not None:
                 mu_t = torch.as_tensor(mu, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
@@ -190,7 +190,7 @@ class HgaEngine:
         if x.shape[1] != self.n_channels:
             raise ValueError(f"expected {self.n_channels} channels, got {x.shape[1]}")
         frames = self.stream_frames(x.shape[0])
-        out = np.empty((frames, self.n_channels), dtype=np.float64)
+        out = np.empty((max(frames, 1), self.n_channels), dtype=np.float64)[:frames]
         mu_h, sg_h = _musigma_host(mu, sigma, self.n_channels)
         check(self._lib.hga_stream_push_host(self._h, x.ctypes.data, x.shape[0], x.strides[0] // 8,
                                              mu_h.ctypes.data if mu_h is not None else None,

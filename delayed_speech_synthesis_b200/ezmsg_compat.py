@@ -73,9 +73,12 @@ except ImportError:
         ezmsg's `Unit.setup()` does before the graph starts."""
 
         def __init__(self, settings=None):
-            ann = {}
-            for klass in reversed(type(self).__mro__):
-                ann.update(getattr(klass, "__annotations__", {}))
+            import typing
+
+            try:
+                ann = typing.get_type_hints(type(self))
+            except Exception:
+                ann = {}
             state_t = ann.get("STATE")
             self.STATE = state_t() if isinstance(state_t, type) else None
             self.SETTINGS = None

@@ -66,6 +66,8 @@ def log_power(data, sr: int, window_length: float, window_shift: float, mu=None,
     F = len(start)
     dev = _dev_index(d)
     out = torch.empty((F, Cn), dtype=torch.float64, device=d.device)
+    if F == 0:
+        return out.cpu().numpy() if as_numpy else out
     regular = filters.windows_are_regular(start, stop, L, hop, rows + zero_rows)
     sd = ed = None
     if not regular:
@@ -98,6 +100,8 @@ def zscore(features, mu, sigma):
     mu_t = torch.as_tensor(mu, dtype=torch.float64, device=f.device).reshape(-1).expand(Cn).contiguous()
     sg_t = torch.as_tensor(sigma, dtype=torch.float64, device=f.device).reshape(-1).expand(Cn).contiguous()
     out = torch.empty((F, Cn), dtype=torch.float64, device=f.device)
+    if F == 0:
+        return out.cpu().numpy() if as_numpy else out
     with torch.cuda.device(dev):
         check(_lib.load().hga_zscore(dev, f.data_ptr(), F, Cn, max(f.stride(0), Cn), mu_t.data_ptr(), sg_t.data_ptr(),
                                      out.data_ptr(), Cn, _stream_ptr(dev)))
@@ -122,6 +126,8 @@ class ChannelStats:
             raise ValueError(f"expected (F, {self.n_channels}) features, got {tuple(f.shape)}")
         if f.stride(1) != 1:
             f = f.contiguous()
+        if f.shape[0] == 0:
+            return self
         with torch.cuda.device(self.device):
             check(_lib.load().hga_stats_accumulate(self.device, f.data_ptr(), f.shape[0], self.n_channels,
                                                    max(f.stride(0), self.n_channels), self.acc.data_ptr(),

@@ -1,0 +1,114 @@
+"""Generate tests/golden/*.npz by EXECUTING the reference in this container (needs /root/reference; run once, commit
+the outputs).  Nothing here is imported by the product.
+
+  python tests/golden/make_golden.py
+
+Pieces executed:
+  * the reference's compiled extension (oracle/_ref, built from /root/reference/extensions/hga/hga_optimized.pyx):
+    compute_log_power_features, and WarmStartFrameBuffer in a keep-alive subprocess (under Cython 3.3 the class aborts
+    when a returned slice is released, SURVEY.md §8c — so every returned object is kept and the child leaves via
+    os._exit);
+  * scipy.signal.sosfilt / sosfilt_zi / iirfilter (the third-party code the reference calls, local/units.py:124-152);
+  * the composition of local/units.py:145-161 written out literally with those pieces.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+ROOT = HERE.parents[1]
+sys.path.insert(0, str(ROOT))
+
+CHILD = r"""
+import os, sys, numpy as np
+sys.path.insert(0, {root!r})
+from oracle import build_ref
+ref = build_ref.load()
+rng = np.random.Generator(np.random.Philox(key=[7, 0]))
+chunks = {chunks!r}
+C = {C}
+fb = ref.WarmStartFrameBuffer(0.05, 0.01, 1000, C)
+keep, outs, ins = [], [], []
+for n in chunks:
+    d = rng.standard_normal((n, C))
+    r = fb.insert(d)
+    keep.append(r); keep.append(d)
+    ins.append(d); outs.append(np.array(r, dtype=np.float64, copy=True))
+np.savez({out!r}, chunks=np.array(chunks), **{{f"in{{i}}": a for i, a in enumerate(ins)}}, **{{f"out{{i}}": a for i, a in enumerate(outs)}})
+sys.stdout.flush()
+os._exit(0)
+"""
+
+
+def framebuffer_golden():
+    for name, chunks, C in (("framebuffer_a", [10, 10, 10, 20, 40, 40, 70], 3), ("framebuffer_b", [60, 10, 25, 13], 2),
+                            ("framebuffer_c", [7, 9, 33, 10], 2)):
+        out = str(HERE / f"{name}.npz")
+        code = CHILD.format(root=str(ROOT), chunks=chunks, C=C, out=out)
+        subprocess.run([sys.executable, "-c", code], check=True)
+
+
+def main():
+    from scipy.signal import iirfilter, sosfilt, sosfilt_zi
+    from oracle import build_ref
+
+    ref = build_ref.load()
+    assert ref is not None, "reference extension unavailable (needs /root/reference)"
+    rng = np.random.Generator(np.random.Philox(key=[20241104, 99]))
+
+    # 1. compute_log_power_features of the compiled reference
+    lp = {}
+    for i, (rows, C, sr, wl, ws) in enumerate([(1000, 4, 1000, 0.05, 0.01), (50, 2, 1000, 0.05, 0.01), (257, 5, 1000, 0.05, 0.01),
+                                               (600, 3, 2000, 0.05, 0.01), (700, 2, 1000, 0.05, 0.0125), (333, 2, 1000, 0.032, 0.008)]):
+        d = rng.standard_normal((rows, C)) * (1.0 + i)
+        lp[f"in{i}"], lp[f"par{i}"] = d, np.array([sr, wl, ws])
+        lp[f"out{i}"] = np.array(ref.compute_log_power_features(d, sr, wl, ws))
+    np.savez(HERE / "log_power.npz", **lp)
+
+    # 2. filters: design, zi, sosfilt outputs and final states (scipy as installed here: see versions below)
+    import scipy
+    filt = {"scipy_version": np.array(scipy.__version__)}
+    for fs in (1000, 2000):
+        nyq = fs / 2
+        bp = iirfilter(8, np.array([70, 170]) / nyq, btype="bandpass", ftype="butter", output="sos")
+        nt = iirfilter(8, np.array([118, 122]) / nyq, btype="bandstop", ftype="butter", output="sos")
+        x = rng.standard_normal((400, 3))
+        zb = np.repeat(sosfilt_zi(bp), 3, axis=-1).reshape(8, 2, 3)
+        zn = np.repeat(sosfilt_zi(nt), 3, axis=-1).reshape(8, 2, 3)
+        y1, s1 = sosfilt(bp, x, axis=0, zi=zb)
+        y2, s2 = sosfilt(nt, y1, axis=0, zi=zn)
+        filt.update({f"bp{fs}": bp, f"nt{fs}": nt, f"zib{fs}": sosfilt_zi(bp), f"zin{fs}": sosfilt_zi(nt), f"x{fs}": x,
+                     f"y1_{fs}": y1, f"s1_{fs}": s1, f"y2_{fs}": y2, f"s2_{fs}": s2})
+    np.savez(HERE / "filters.npz", **filt)
+
+    # 3. the whole path, local/units.py:145-161 literally: offline single call and 10-sample packets, + z-score
+    fs, C, T = 1000, 6, 1200
+    x = rng.standard_normal((T, C)) * 30 + 20 * np.sin(2 * np.pi * 120 * np.arange(T) / fs)[:, None]
+    bp, nt = filt["bp1000"], filt["nt1000"]
+    zb = np.repeat(sosfilt_zi(bp), C, axis=-1).reshape(8, 2, C)
+    zn = np.repeat(sosfilt_zi(nt), C, axis=-1).reshape(8, 2, C)
+    d, _ = sosfilt(bp, x, axis=0, zi=zb)
+    d, _ = sosfilt(nt, d, axis=0, zi=zn)                       # frame buffer case 1: data passes through unchanged
+    off = np.array(ref.compute_log_power_features(d, fs, 0.05, 0.01))
+    mu, sd = np.mean(off, axis=0), np.std(off, axis=0)         # prepare_corpus.py:198-199
+    # streaming: case 2 then case 3 (restated buffer; framebuffer_*.npz pins the restatement against the compiled class)
+    hs, fh, rem, first, frames = zb.copy(), zn.copy(), np.zeros((40, C)), True, []
+    for t in range(0, 300, 10):
+        c, hs = sosfilt(bp, x[t:t + 10], axis=0, zi=hs)
+        c, fh = sosfilt(nt, c, axis=0, zi=fh)
+        buf = np.concatenate([np.zeros((40, C)), c]) if first else np.concatenate([rem, c])
+        first, rem = False, buf[-40:]
+        frames.append(np.array(ref.compute_log_power_features(np.ascontiguousarray(buf), fs, 0.05, 0.01)))
+    np.savez(HERE / "pipeline.npz", x=x, offline=off, mu=mu, sigma=sd, offline_z=(off - mu) / sd,
+             stream=np.concatenate(frames), stream_hg_state=hs, stream_fh_state=fh)
+    framebuffer_golden()
+    print("golden written:", sorted(p.name for p in HERE.glob("*.npz")))
+
+
+if __name__ == "__main__":
+    main()
