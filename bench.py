@@ -248,6 +248,8 @@ def run_b200(args):
     # ---- end to end through the host-buffer C-ABI call: pinned host input, host output, copies inside the timed region
     e2e = None
     try:
+        if args.no_e2e:
+            raise RuntimeError('skipped (--no-e2e)')
         xh = torch.empty((T, C), dtype=torch.float64, pin_memory=True)
         xh.copy_(x)
         oh = torch.empty((F, C), dtype=torch.float64, pin_memory=True)
@@ -289,7 +291,7 @@ def run_b200(args):
         traffic = json.loads(tp.read_text()).get(args.workload)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
         "data": "synthetic",
         "config": {"workload": workload_name(args.workload), "precision": args.precision, "warmup_samples": eng.warmup,
                    "l2": "input 3.69 GB per step > 126 MB L2 (no flush needed)" if args.workload != "k1" else "k1 fits L2",
@@ -311,7 +313,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="k2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="f64", choices=["f64", "exact"])
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32", "exact"])
+    ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -9,8 +9,8 @@ from . import _build
 
 HGA_ABI_VERSION = 1
 HGA_MAX_SECTIONS = 8
-PREC_EXACT, PREC_F64 = 0, 1
-PRECISIONS = {"exact": PREC_EXACT, "f64": PREC_F64}
+PREC_EXACT, PREC_F64, PREC_F32 = 0, 1, 2
+PRECISIONS = {"exact": PREC_EXACT, "f64": PREC_F64, "f32": PREC_F32}
 
 
 class HgaError(RuntimeError):

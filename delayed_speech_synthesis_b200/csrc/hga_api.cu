@@ -150,10 +150,107 @@ static double max_pole_radius(const Cascade& q) {
   return r;
 }
 
+// ------------------------------------------------------------------------------------------------ pipe kernel host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+    }
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+static void build_pipe_const(const Cascade& q, int L, PipeConst& pc) {
+  memset(&pc, 0, sizeof pc);
+  double G = 1.0;
+  for (int s = 0; s < q.ns; ++s) {
+    G *= q.g[s];
+    pc.zu0[s] = q.zi0[s] / G;
+    pc.zu1[s] = q.zi1[s] / G;
+    pc.a1f[s] = (float)q.a1[s];
+    pc.a2f[s] = (float)q.a2[s];
+    pc.b1uf[s] = (float)q.b1u[s];
+  }
+  pc.pow_scale = G * G / (double)L;
+}
+struct PipeShape {
+  int S, TB;
+};
+static PipeShape pipe_shape() {
+  PipeShape p{4, 40};
+  if (const char* e = getenv("HGA_B200_PIPE_S")) p.S = atoi(e);
+  if (const char* e = getenv("HGA_B200_PIPE_TB")) p.TB = atoi(e);
+  if (p.S != 2 && p.S != 4 && p.S != 8) p.S = 4;
+  if (p.TB != 20 && p.TB != 40) p.TB = 40;
+  return p;
+}
+template <typename T, int S, int TB>
+static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
+  auto kern = k_hga_pipe<T, S, TB>;
+  const int smem = (int)PipeSmem<S, TB, T>::total;
+  static bool attr_done = false;
+  if (!attr_done) {
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_done = true;
+  }
+  if (occ) {
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, 32 * S, smem));
+    return HGA_OK;
+  }
+  const int cg = (a.C + 31) / 32;
+  kern<<<(unsigned)((int64_t)a.n_work * cg), 32 * S, smem, st>>>(q, pc, a, tm);
+  LAUNCHED();
+  return HGA_OK;
+}
+// occ != nullptr: only query the resident CTAs per SM of the variant that would be launched.
+template <typename T>
+static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
+  const PipeShape p = pipe_shape();
+  if (p.S == 2 && p.TB == 40) return pipe_launch_t<T, 2, 40>(q, pc, a, tm, st, occ);
+  if (p.S == 2 && p.TB == 20) return pipe_launch_t<T, 2, 20>(q, pc, a, tm, st, occ);
+  if (p.S == 4 && p.TB == 20) return pipe_launch_t<T, 4, 20>(q, pc, a, tm, st, occ);
+  if (p.S == 8 && p.TB == 40) return pipe_launch_t<T, 8, 40>(q, pc, a, tm, st, occ);
+  if (p.S == 8 && p.TB == 20) return pipe_launch_t<T, 8, 20>(q, pc, a, tm, st, occ);
+  return pipe_launch_t<T, 4, 40>(q, pc, a, tm, st, occ);
+}
+static bool pipe_supported(const Cascade& q, int hop, int nb) {
+  return is_unit_std(q) && (hop == 10 || hop == 20) && nb >= 1 && nb <= 8 && encode_tiled_fn() != nullptr;
+}
+// x must be 16-byte aligned with an even leading dimension for the TMA descriptor
+static bool pipe_layout_ok(const double* x, int64_t ldx) { return ((uintptr_t)x % 16) == 0 && (ldx % 2) == 0; }
+static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, const FusedArgs& a, cudaStream_t st) {
+  CUtensorMap tm;
+  const cuuint64_t dims[2] = {(cuuint64_t)a.C, (cuuint64_t)(a.x_row_hi - a.x_row_lo)};
+  const cuuint64_t strides[1] = {(cuuint64_t)a.ldx * 8};
+  const PipeShape p = pipe_shape();
+  const cuuint32_t box[2] = {32, (cuuint32_t)p.TB};
+  const cuuint32_t es[2] = {1, 1};
+  void* base = (void*)(a.x + a.x_row_lo * a.ldx);
+  const CUresult r = encode_tiled_fn()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(HGA_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, tm, st, nullptr);
+}
+static int64_t pipe_item_slots(const Cascade& q, const PipeConst& pc, int precision, int n_sm, int C) {
+  int occ = 1;
+  FusedArgs a{};
+  CUtensorMap tm{};
+  if ((precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, tm, nullptr, &occ) : pipe_dispatch<double>(q, pc, a, tm, nullptr, &occ)) != HGA_OK) occ = 1;
+  if (const char* e = getenv("HGA_B200_PIPE_OCC")) occ = std::max(1, std::min(occ, atoi(e)));
+  return std::max<int64_t>(1, (int64_t)n_sm * std::max(1, occ) / ((C + 31) / 32));
+}
+
 // ------------------------------------------------------------------------------------------------ the handle
 struct hga_handle {
   hga_config cfg;
   Cascade q;
+  PipeConst pc;
   int n_sm = 0;
   int warmup = 0;
   int overlap = 0;   // L - hop
@@ -205,7 +302,7 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   if (cfg->n_sections_bp < 1 || cfg->n_sections_bp > HGA_MAX_SECTIONS || cfg->n_sections_notch < 0 ||
       cfg->n_sections_notch > HGA_MAX_SECTIONS)
     return fail(HGA_ERR_INVALID, "bad section counts %d/%d", cfg->n_sections_bp, cfg->n_sections_notch);
-  if (cfg->precision != HGA_PREC_EXACT && cfg->precision != HGA_PREC_F64) return fail(HGA_ERR_INVALID, "bad precision %d", cfg->precision);
+  if (cfg->precision != HGA_PREC_EXACT && cfg->precision != HGA_PREC_F64 && cfg->precision != HGA_PREC_F32) return fail(HGA_ERR_INVALID, "bad precision %d", cfg->precision);
   if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
   if (cfg->device < 0 || cfg->device >= hga_device_count()) return fail(HGA_ERR_INVALID, "bad device %d", cfg->device);
   CU(cudaSetDevice(cfg->device));
@@ -213,6 +310,7 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   h->cfg = *cfg;
   int rc = build_cascade(h->q, cfg->sos_bp, cfg->n_sections_bp, cfg->zi_bp, cfg->sos_notch, cfg->n_sections_notch, cfg->zi_notch);
   if (rc) { delete h; return rc; }
+  build_pipe_const(h->q, cfg->frame_len, h->pc);
   cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, cfg->device);
   h->overlap = cfg->frame_len - cfg->hop;
   h->nb = (cfg->frame_len % cfg->hop == 0 && cfg->frame_len / cfg->hop <= kMaxBlocksPerFrame) ? cfg->frame_len / cfg->hop : 0;
@@ -220,7 +318,7 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   if (r >= 1.0) { delete h; return fail(HGA_ERR_INVALID, "unstable filter: pole radius %g", r); }
   if (cfg->warmup > 0) h->warmup = cfg->warmup;
   else {
-    const double tol = cfg->warmup_tol > 0 ? cfg->warmup_tol : 1e-10;
+    const double tol = cfg->warmup_tol > 0 ? cfg->warmup_tol : (cfg->precision == HGA_PREC_F32 ? 1e-7 : 1e-12);
     h->warmup = r > 0 ? (int)std::ceil(std::log(tol) / std::log(r)) : 1;
   }
   h->warmup = std::max(h->warmup, h->overlap);
@@ -342,11 +440,13 @@ static int upload_plan(hga_handle* h, cudaStream_t st) {
   return HGA_OK;
 }
 
-// Which fused kernel: 0 = thread-per-(item, channel) sequential cascade, 1 = warp-pipelined.
-static int choose_variant(const hga_handle* h, int n_seg, const int64_t* seg_len) {
+// Which fused kernel: 0 = thread-per-(item, channel) sequential cascade (f64 only), 1 = section-pipelined (f64 / f32).
+static int choose_variant(const hga_handle* h, const double* x, int64_t ldx, bool plain) {
+  const bool can_pipe = plain && pipe_supported(h->q, h->cfg.hop, h->nb) && pipe_layout_ok(x, ldx);
+  if (h->cfg.precision == HGA_PREC_F32) return can_pipe ? 1 : -3;
   const char* env = getenv("HGA_B200_VARIANT");
-  if (env && *env) return atoi(env);
-  return pipe_supported(h->q, h->cfg.hop, h->nb) ? pipe_preferred(h->n_sm, h->cfg.n_channels, n_seg, seg_len, h->warmup) : 0;
+  if (env && *env) return (atoi(env) == 1 && can_pipe) ? 1 : 0;
+  return can_pipe ? 1 : 0;
 }
 
 template <int ARITH>
@@ -371,33 +471,37 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
   for (int i = 0; i < n_seg; ++i)
     if (seg_len[i] < L && !allow_short) return fail(HGA_ERR_INVALID, "segment %d has %lld rows < frame_len %d", i, (long long)seg_len[i], L);
   int rc;
-  const bool fused = h->cfg.precision == HGA_PREC_F64 && h->nb > 0;
+  const bool fused = (h->cfg.precision == HGA_PREC_F64 || h->cfg.precision == HGA_PREC_F32) && h->nb > 0;
   // plan (cached on the segment table)
   std::vector<int64_t> key;
   key.reserve(3 * (size_t)n_seg + 1);
   key.insert(key.end(), seg_start, seg_start + n_seg);
   key.insert(key.end(), seg_len, seg_len + n_seg);
   key.insert(key.end(), out_row, out_row + n_seg);
-  const int variant = fused ? choose_variant(h, n_seg, seg_len) : -2;
+  const bool plain = !state_in && !rem_in && !state_out && !rem_out;
+  const int variant = fused ? choose_variant(h, x, ldx, plain) : -2;
+  if (variant == -3) return fail(HGA_ERR_UNSUPPORTED, "f32 precision needs the standard 8+8-section unit-gain cascade, hop 10 or 20, "
+                                                      "16-byte-aligned x with an even leading dimension, and no carried state");
   if (key != h->plan_key || variant != h->plan_variant) {
     const int cg = (C + 31) / 32;
     int64_t slots = 0;
     if (variant == 0) slots = std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
-    else if (variant == 1) slots = pipe_item_slots(h->n_sm, C);
+    else if (variant == 1) slots = pipe_item_slots(h->q, h->pc, h->cfg.precision, h->n_sm, C);
     plan_chunks(h, n_seg, seg_start, seg_len, out_row, slots, fused);
     if ((rc = upload_plan(h, st))) return rc;
     h->plan_key = key;
     h->plan_variant = variant;
   }
   if (fused) {
-    FusedArgs a{x, ldx, h->work.as<Work>(), (int)h->work_host.size(), C, L, hop, h->nb, h->cfg.eps, mu, sigma, out, ldo, state_in, rem_in, state_out, rem_out};
+    int64_t xlo = INT64_MAX, xhi = 0;
+    for (int i = 0; i < n_seg; ++i) { xlo = std::min(xlo, seg_start[i]); xhi = std::max(xhi, seg_start[i] + seg_len[i]); }
+    FusedArgs a{x, ldx, h->work.as<Work>(), (int)h->work_host.size(), C, L, hop, h->nb, h->cfg.eps, mu, sigma, out, ldo, state_in, rem_in, state_out, rem_out, xlo, xhi};
     if (h->timing) CU(cudaEventRecord(h->ev0, st));
-    if (variant == 1) rc = launch_pipe(h->q, a, h->n_sm, st);
+    if (variant == 1) rc = launch_pipe(h->q, h->pc, h->cfg.precision, a, st);
     else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, st);
     else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, st);
     else rc = launch_fused_seq<kFused>(h, a, st);
     if (rc) return rc;
-    if (variant == 1) LAUNCHED();
     if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; }
     return HGA_OK;
   }
@@ -750,7 +854,7 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
   if ((rc = sync_musigma(h, mu_host, sigma_host, sk, &mu_d, &sig_d))) return rc;
   double* xd = h->xdev.as<double>() - lo * C;     // device row r <-> host row r
   double* od = h->outdev.as<double>() - olo * C;  // device out row r <-> host out row r
-  const bool fused = h->cfg.precision == HGA_PREC_F64 && h->nb > 0;
+  const bool fused = (h->cfg.precision == HGA_PREC_F64 || h->cfg.precision == HGA_PREC_F32) && h->nb > 0;
 
   if (!fused) {
     CU(cudaMemcpy2DAsync(xd + lo * C, row_bytes, x_host + lo * ldx, (size_t)ldx * 8, row_bytes, (size_t)(hi - lo), cudaMemcpyHostToDevice, sk));
@@ -765,10 +869,11 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     key.insert(key.end(), seg_start, seg_start + n_segments);
     key.insert(key.end(), seg_len, seg_len + n_segments);
     key.insert(key.end(), out_row, out_row + n_segments);
-    const int variant = choose_variant(h, n_segments, seg_len);
+    const int variant = choose_variant(h, xd + lo * C, C, true);
+    if (variant == -3) return fail(HGA_ERR_UNSUPPORTED, "f32 precision needs the standard 8+8-section unit-gain cascade and hop 10 or 20");
     if (key != h->plan_key || variant != h->plan_variant) {
       const int cg = (C + 31) / 32;
-      const int64_t slots = variant == 1 ? pipe_item_slots(h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
+      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->pc, h->cfg.precision, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
       plan_chunks(h, n_segments, seg_start, seg_len, out_row, slots, true);
       if ((rc = upload_plan(h, sk))) return rc;
       h->plan_key = key;
@@ -797,8 +902,8 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     cudaEvent_t e_up = h->slab_ev[ev++];
     CU(cudaEventRecord(e_up, sc));
     CU(cudaStreamWaitEvent(sk, e_up, 0));
-    FusedArgs a{xd, C, h->work.as<Work>() + next, (int)(end - next), C, L, hop, h->nb, h->cfg.eps, mu_d, sig_d, od, C, nullptr, nullptr, nullptr, nullptr};
-    if (variant == 1) { if ((rc = launch_pipe(h->q, a, h->n_sm, sk))) return rc; LAUNCHED(); }
+    FusedArgs a{xd, C, h->work.as<Work>() + next, (int)(end - next), C, L, hop, h->nb, h->cfg.eps, mu_d, sig_d, od, C, nullptr, nullptr, nullptr, nullptr, lo, hi};
+    if (variant == 1) rc = launch_pipe(h->q, h->pc, h->cfg.precision, a, sk);
     else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, sk);
     else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, sk);
     else rc = launch_fused_seq<kFused>(h, a, sk);

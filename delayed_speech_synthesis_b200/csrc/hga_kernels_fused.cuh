@@ -81,6 +81,7 @@ struct FusedArgs {
   const double* remainder_in;  // (L - hop, C) or nullptr: filtered rows preceding row 0 (frame-buffer case 3)
   double* state_out;      // (n_segs, ns, 2, C) or nullptr
   double* remainder_out;  // (n_segs, L - hop, C) or nullptr: last L-hop filtered rows of each segment
+  int64_t x_row_lo, x_row_hi;  // rows [x_row_lo, x_row_hi) of x are addressable (TMA extents of the pipe kernel)
 };
 
 // Thread per (work item, channel); a warp spans 32 adjacent channels so every row access is one 256-byte segment.

@@ -44,7 +44,12 @@ enum hga_precision {
   HGA_PREC_EXACT = 0,
   /* float64 with fused multiply-adds, time-chunked (each chunk re-filters `warmup` samples of history from zero
    * state), window power as the sum of hop-block partial sums.  |feature - reference| <= 1e-9 (tests state it). */
-  HGA_PREC_F64 = 1
+  HGA_PREC_F64 = 1,
+  /* float32 cascade arithmetic on the float64 input (converted after the load), float64 power sums / log / z-score,
+   * same time-chunking as HGA_PREC_F64.  Offline extraction only (streaming pushes keep HGA_PREC_EXACT arithmetic).
+   * |feature - reference| <= 1e-4 on white / ECoG-like input (tests state it; typical max 2e-5).  Needs the standard
+   * cascade (8 + 8 unit-numerator sections), hop 10 or 20, x 16-byte aligned with an even leading dimension. */
+  HGA_PREC_F32 = 2
 };
 
 /* Configuration of one extractor = the constructor arguments of HighGammaExtractor (local/units.py:102-132) after the
@@ -67,7 +72,7 @@ typedef struct hga_config {
   int32_t precision;                     /* enum hga_precision: arithmetic of hga_extract_offline* */
   int32_t warmup;                        /* HGA_PREC_F64: history re-filtered per time-chunk; 0 = derive from
                                             warmup_tol and the largest pole radius */
-  double warmup_tol;                     /* target truncation error of the warm-up (default 1e-10 when 0) */
+  double warmup_tol;                     /* target truncation error of the warm-up (0 = default: 1e-12 for F64, 1e-7 for F32) */
   int32_t max_push_rows;                 /* largest n accepted by hga_stream_push (0 = 4096) */
   int32_t reserved;
 } hga_config;

@@ -6,6 +6,8 @@ inputs.  Tolerances (stated here, per feature = per (frame, channel) element):
     <= 5e-9 on z-scores (division by sigma ~ 0.4); relative error <= 1e-8 where |f| > 1e-2.
   * filtered samples (hga_sosfilt) and filter states: bit-identical to scipy.signal.sosfilt.
   * baseline mu / sigma: relative error <= 1e-12.
+  * 'f32' precision (float32 cascade arithmetic, float64 power sums): max-abs <= 1e-4 on features (observed ~2e-5),
+    <= 5e-4 on z-scores.
 """
 import numpy as np
 import pytest
@@ -17,6 +19,7 @@ from oracle import c_oracle as CO  # noqa: E402
 
 TOL_EXACT = 4e-15
 TOL_F64 = 1e-9
+TOL_F32 = 1e-4
 
 
 def _oracle_offline(x, fs, mu=None, sigma=None, segments=None):
@@ -152,6 +155,42 @@ def test_offline_time_chunked_long(torch):
     got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
     a, r = _err(got, ref)
     assert a <= TOL_F64, (a, r)
+
+
+@pytest.mark.parametrize("variant,S,TB", [("0", "4", "40"), ("1", "4", "40"), ("1", "2", "40"), ("1", "8", "20"), ("1", "4", "20")])
+def test_offline_kernel_variants_agree(variant, S, TB, torch, monkeypatch):
+    """The thread-sequential and the section-pipelined kernels (every warps-per-item / tile shape) against the oracle:
+    ragged segments (partial tiles, lengths that are not hop multiples), C not a multiple of 32, z-score."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    monkeypatch.setenv("HGA_B200_VARIANT", variant)
+    monkeypatch.setenv("HGA_B200_PIPE_S", S)
+    monkeypatch.setenv("HGA_B200_PIPE_TB", TB)
+    fs, C = 1000, 70
+    x = O.synthetic_ecog(90007, C, fs, "ecog", session=11)
+    segs = [(0, 50), (50, 2590), (2600, 2655), (3000, 9017), (9018, 90007)]
+    base = _oracle_offline(x, fs, segments=segs)
+    mu, sigma = base.mean(0), base.std(0)
+    ref = _oracle_offline(x, fs, mu, sigma, segments=segs)
+    got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda(), segs, mu, sigma).cpu().numpy()
+    assert got.shape == ref.shape
+    assert _err(got, ref)[0] <= 5 * TOL_F64
+
+
+@pytest.mark.parametrize("kind", ["white", "ecog"])
+def test_offline_f32_mode(kind, torch):
+    """float32 cascade arithmetic: stated tolerance 1e-4 max-abs per feature (log-power), 5e-4 per z-score."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, C = 1000, 200000, 128
+    x = O.synthetic_ecog(T, C, fs, kind, session=12)
+    ref = _oracle_offline(x, fs)
+    mu, sigma = ref.mean(0), ref.std(0)
+    eng = HgaEngine(fs, C, precision="f32")
+    got = eng.extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    a, r = _err(got, ref)
+    assert a <= TOL_F32, (a, r)
+    z = eng.extract_offline(torch.from_numpy(x).cuda(), None, mu, sigma).cpu().numpy()
+    assert np.abs(z - (ref - mu) / sigma).max() <= 5 * TOL_F32
+    assert np.array_equal(eng.extract_offline(x), got)          # host-buffer path == device path
 
 
 def test_offline_2khz_high_density_prefix(torch):
