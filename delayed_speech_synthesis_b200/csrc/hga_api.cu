@@ -186,13 +186,13 @@ static PipeShape pipe_shape() {
   PipeShape p{4, 40};
   if (const char* e = getenv("HGA_B200_PIPE_S")) p.S = atoi(e);
   if (const char* e = getenv("HGA_B200_PIPE_TB")) p.TB = atoi(e);
-  if (p.S != 2 && p.S != 4 && p.S != 8) p.S = 4;
-  if (p.TB != 20 && p.TB != 40) p.TB = 40;
+  if (p.S != 2 && p.S != 4) p.S = 4;
+  if (p.TB != 20 || p.S != 4) p.TB = 40;
   return p;
 }
-template <typename T, int S, int TB>
+template <typename T, int S, int TB, int HOP>
 static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
-  auto kern = k_hga_pipe<T, S, TB>;
+  auto kern = k_hga_pipe<T, S, TB, HOP>;
   const int smem = (int)PipeSmem<S, TB, T>::total;
   static bool attr_done = false;
   if (!attr_done) {
@@ -200,24 +200,25 @@ static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs&
     attr_done = true;
   }
   if (occ) {
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, 32 * S, smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, 64 * S, smem));
     return HGA_OK;
   }
   const int cg = (a.C + 31) / 32;
-  kern<<<(unsigned)((int64_t)a.n_work * cg), 32 * S, smem, st>>>(q, pc, a, tm);
+  kern<<<(unsigned)((int64_t)a.n_work * cg), 64 * S, smem, st>>>(q, pc, a, tm);
   LAUNCHED();
   return HGA_OK;
 }
 // occ != nullptr: only query the resident CTAs per SM of the variant that would be launched.
 template <typename T>
-static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
+static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs& a, int hop, const CUtensorMap& tm, cudaStream_t st, int* occ) {
   const PipeShape p = pipe_shape();
-  if (p.S == 2 && p.TB == 40) return pipe_launch_t<T, 2, 40>(q, pc, a, tm, st, occ);
-  if (p.S == 2 && p.TB == 20) return pipe_launch_t<T, 2, 20>(q, pc, a, tm, st, occ);
-  if (p.S == 4 && p.TB == 20) return pipe_launch_t<T, 4, 20>(q, pc, a, tm, st, occ);
-  if (p.S == 8 && p.TB == 40) return pipe_launch_t<T, 8, 40>(q, pc, a, tm, st, occ);
-  if (p.S == 8 && p.TB == 20) return pipe_launch_t<T, 8, 20>(q, pc, a, tm, st, occ);
-  return pipe_launch_t<T, 4, 40>(q, pc, a, tm, st, occ);
+  if (hop == 10) {
+    if (p.S == 2) return pipe_launch_t<T, 2, 40, 10>(q, pc, a, tm, st, occ);
+    if (p.TB == 20) return pipe_launch_t<T, 4, 20, 10>(q, pc, a, tm, st, occ);
+    return pipe_launch_t<T, 4, 40, 10>(q, pc, a, tm, st, occ);
+  }
+  if (p.S == 2) return pipe_launch_t<T, 2, 40, 20>(q, pc, a, tm, st, occ);
+  return pipe_launch_t<T, 4, 40, 20>(q, pc, a, tm, st, occ);
 }
 static bool pipe_supported(const Cascade& q, int hop, int nb) {
   return is_unit_std(q) && (hop == 10 || hop == 20) && nb >= 1 && nb <= 8 && encode_tiled_fn() != nullptr;
@@ -235,13 +236,37 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
   const CUresult r = encode_tiled_fn()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(HGA_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
-  return precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, tm, st, nullptr);
+  if (getenv("HGA_B200_PROF")) {  // debugging aid: per-warp cycle breakdown, printed to stderr (synchronises)
+    const size_t n_cta = (size_t)a.n_work * ((a.C + 31) / 32), n = n_cta * 8 * 6;
+    long long* d = nullptr;
+    CU(cudaMalloc(&d, n * 8));
+    CU(cudaMemset(d, 0, n * 8));
+    FusedArgs b = a;
+    b.prof = d;
+    int rc = precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, b, b.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, b, b.hop, tm, st, nullptr);
+    CU(cudaStreamSynchronize(st));
+    std::vector<long long> hbuf(n);
+    CU(cudaMemcpy(hbuf.data(), d, n * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    const char* names[6] = {"role", "tma_wait", "phaseA", "phaseB", "barrier", "total"};
+    for (int g = 0; g < 8; ++g) {
+      double acc[6] = {0};
+      for (size_t cta = 0; cta < n_cta; ++cta)
+        for (int i = 0; i < 6; ++i) acc[i] += (double)hbuf[(cta * 8 + g) * 6 + i];
+      if (acc[5] == 0) continue;
+      fprintf(stderr, "[hga prof] warp %d:", g);
+      for (int i = 0; i < 6; ++i) fprintf(stderr, " %s=%.0f", names[i], acc[i] / n_cta);
+      fprintf(stderr, "  (cycles per CTA, mean of %zu CTAs)\n", n_cta);
+    }
+    return rc;
+  }
+  return precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, a.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, a.hop, tm, st, nullptr);
 }
-static int64_t pipe_item_slots(const Cascade& q, const PipeConst& pc, int precision, int n_sm, int C) {
+static int64_t pipe_item_slots(const Cascade& q, const PipeConst& pc, int precision, int hop, int n_sm, int C) {
   int occ = 1;
   FusedArgs a{};
   CUtensorMap tm{};
-  if ((precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, tm, nullptr, &occ) : pipe_dispatch<double>(q, pc, a, tm, nullptr, &occ)) != HGA_OK) occ = 1;
+  if ((precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, hop, tm, nullptr, &occ) : pipe_dispatch<double>(q, pc, a, hop, tm, nullptr, &occ)) != HGA_OK) occ = 1;
   if (const char* e = getenv("HGA_B200_PIPE_OCC")) occ = std::max(1, std::min(occ, atoi(e)));
   return std::max<int64_t>(1, (int64_t)n_sm * std::max(1, occ) / ((C + 31) / 32));
 }
@@ -486,7 +511,7 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
     const int cg = (C + 31) / 32;
     int64_t slots = 0;
     if (variant == 0) slots = std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
-    else if (variant == 1) slots = pipe_item_slots(h->q, h->pc, h->cfg.precision, h->n_sm, C);
+    else if (variant == 1) slots = pipe_item_slots(h->q, h->pc, h->cfg.precision, h->cfg.hop, h->n_sm, C);
     plan_chunks(h, n_seg, seg_start, seg_len, out_row, slots, fused);
     if ((rc = upload_plan(h, st))) return rc;
     h->plan_key = key;
@@ -495,7 +520,7 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
   if (fused) {
     int64_t xlo = INT64_MAX, xhi = 0;
     for (int i = 0; i < n_seg; ++i) { xlo = std::min(xlo, seg_start[i]); xhi = std::max(xhi, seg_start[i] + seg_len[i]); }
-    FusedArgs a{x, ldx, h->work.as<Work>(), (int)h->work_host.size(), C, L, hop, h->nb, h->cfg.eps, mu, sigma, out, ldo, state_in, rem_in, state_out, rem_out, xlo, xhi};
+    FusedArgs a{x, ldx, h->work.as<Work>(), (int)h->work_host.size(), C, L, hop, h->nb, h->cfg.eps, mu, sigma, out, ldo, state_in, rem_in, state_out, rem_out, xlo, xhi, nullptr};
     if (h->timing) CU(cudaEventRecord(h->ev0, st));
     if (variant == 1) rc = launch_pipe(h->q, h->pc, h->cfg.precision, a, st);
     else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, st);
@@ -873,7 +898,7 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     if (variant == -3) return fail(HGA_ERR_UNSUPPORTED, "f32 precision needs the standard 8+8-section unit-gain cascade and hop 10 or 20");
     if (key != h->plan_key || variant != h->plan_variant) {
       const int cg = (C + 31) / 32;
-      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->pc, h->cfg.precision, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
+      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->pc, h->cfg.precision, h->cfg.hop, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
       plan_chunks(h, n_segments, seg_start, seg_len, out_row, slots, true);
       if ((rc = upload_plan(h, sk))) return rc;
       h->plan_key = key;
@@ -902,7 +927,7 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     cudaEvent_t e_up = h->slab_ev[ev++];
     CU(cudaEventRecord(e_up, sc));
     CU(cudaStreamWaitEvent(sk, e_up, 0));
-    FusedArgs a{xd, C, h->work.as<Work>() + next, (int)(end - next), C, L, hop, h->nb, h->cfg.eps, mu_d, sig_d, od, C, nullptr, nullptr, nullptr, nullptr, lo, hi};
+    FusedArgs a{xd, C, h->work.as<Work>() + next, (int)(end - next), C, L, hop, h->nb, h->cfg.eps, mu_d, sig_d, od, C, nullptr, nullptr, nullptr, nullptr, lo, hi, nullptr};
     if (variant == 1) rc = launch_pipe(h->q, h->pc, h->cfg.precision, a, sk);
     else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, sk);
     else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, sk);

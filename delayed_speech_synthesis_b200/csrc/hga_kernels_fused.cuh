@@ -82,6 +82,7 @@ struct FusedArgs {
   double* state_out;      // (n_segs, ns, 2, C) or nullptr
   double* remainder_out;  // (n_segs, L - hop, C) or nullptr: last L-hop filtered rows of each segment
   int64_t x_row_lo, x_row_hi;  // rows [x_row_lo, x_row_hi) of x are addressable (TMA extents of the pipe kernel)
+  long long* prof;             // optional (HGA_B200_PROF=1): per-warp cycle breakdown of the pipe kernel, [n_cta][8 warps][6]
 };
 
 // Thread per (work item, channel); a warp spans 32 adjacent channels so every row access is one 256-byte segment.

@@ -71,32 +71,82 @@ template <> struct PipeCoef<float> {
   static __device__ __forceinline__ float b1(const Cascade&, const PipeConst& p, int s) { return p.b1uf[s]; }
 };
 
-// `rows` rows of a tile through sections [G*NS, (G+1)*NS): in (row-major, 32 lanes per row) -> out.
-template <typename T, typename TIN, int G, int NS, int RB>
+// One wavefront step: section s in [LO, HI] consumes the output its predecessor produced in the PREVIOUS step (section 0
+// consumes x0), so the NS section updates of a step are mutually independent and the four instruction groups below
+// (adds, numerator FMAs, z0 FMAs, z1 FMAs) keep every dependent pair >= NS issue slots apart: the FP64 pipe's 8-cycle
+// latency at one issue per 2 cycles is covered by a single warp when NS >= 4.  Returns the output of section NS-1.
+template <typename T, int G, int NS, int LO, int HI>
+__device__ __forceinline__ T wave_step(const Cascade& q, const PipeConst& pc, T x0, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
+  using K = PipeCoef<T>;
+  T xin[NS], yn[NS], t[NS];
+#pragma unroll
+  for (int s = LO; s <= HI; ++s) xin[s] = s == 0 ? x0 : yp[s - 1];
+#pragma unroll
+  for (int s = LO; s <= HI; ++s) yn[s] = xin[s] + z0[s];
+#pragma unroll
+  for (int s = LO; s <= HI; ++s) t[s] = fma(K::b1(q, pc, G * NS + s), xin[s], z1[s]);
+#pragma unroll
+  for (int s = LO; s <= HI; ++s) z0[s] = fma(-K::a1(q, pc, G * NS + s), yn[s], t[s]);
+#pragma unroll
+  for (int s = LO; s <= HI; ++s) z1[s] = fma(-K::a2(q, pc, G * NS + s), yn[s], xin[s]);
+#pragma unroll
+  for (int s = LO; s <= HI; ++s) yp[s] = yn[s];
+  return yn[NS - 1];
+}
+template <typename T, int G, int NS, int K0, int K1>  // prologue steps K0..K1-1: sections 0..k active
+struct WaveFill {
+  static __device__ __forceinline__ void run(const Cascade& q, const PipeConst& pc, const T* v, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
+    wave_step<T, G, NS, 0, K0>(q, pc, v[K0], yp, z0, z1);
+    WaveFill<T, G, NS, K0 + 1, K1>::run(q, pc, v, yp, z0, z1);
+  }
+};
+template <typename T, int G, int NS, int K1>
+struct WaveFill<T, G, NS, K1, K1> {
+  static __device__ __forceinline__ void run(const Cascade&, const PipeConst&, const T*, T (&)[NS], T (&)[NS], T (&)[NS]) {}
+};
+template <typename T, int G, int NS, int J, int J1>  // epilogue steps: sections J..NS-1 active, one output each
+struct WaveDrain {
+  static __device__ __forceinline__ void run(const Cascade& q, const PipeConst& pc, T* o, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
+    o[(J - 1) * 32] = wave_step<T, G, NS, J, NS - 1>(q, pc, (T)0, yp, z0, z1);
+    WaveDrain<T, G, NS, J + 1, J1>::run(q, pc, o, yp, z0, z1);
+  }
+};
+template <typename T, int G, int NS, int J1>
+struct WaveDrain<T, G, NS, J1, J1> {
+  static __device__ __forceinline__ void run(const Cascade&, const PipeConst&, T*, T (&)[NS], T (&)[NS], T (&)[NS]) {}
+};
+
+// `rows` rows of a tile through sections [G*NS, (G+1)*NS): in (row-major, 32 lanes per row) -> out.  Full tiles run
+// the skewed wavefront (fill NS-1 steps, TB-NS+1 steady steps, drain NS-1 steps); ragged tiles go row by row.
+template <typename T, typename TIN, int G, int NS, int TB>
 __device__ __forceinline__ void pipe_rows(const Cascade& q, const PipeConst& pc, const TIN* __restrict__ in, T* __restrict__ out,
                                           int rows, T (&z0)[NS], T (&z1)[NS]) {
   using K = PipeCoef<T>;
-  int r = 0;
-  for (; r + RB <= rows; r += RB) {
-    T v[RB];
+  if (rows == TB) {
+    T yp[NS];
+    {
+      T v[NS > 1 ? NS - 1 : 1];
 #pragma unroll
-    for (int i = 0; i < RB; ++i) v[i] = (T)in[(r + i) * 32];
-#pragma unroll
-    for (int i = 0; i < RB; ++i) {
-      T x = v[i];
-#pragma unroll
-      for (int s = 0; s < NS; ++s) {
-        const T y = x + z0[s];
-        z0[s] = fma(-K::a1(q, pc, G * NS + s), y, fma(K::b1(q, pc, G * NS + s), x, z1[s]));
-        z1[s] = fma(-K::a2(q, pc, G * NS + s), y, x);
-        x = y;
-      }
-      v[i] = x;
+      for (int i = 0; i < NS - 1; ++i) v[i] = (T)in[i * 32];
+      WaveFill<T, G, NS, 0, NS - 1>::run(q, pc, v, yp, z0, z1);
     }
+    constexpr int NSTEADY = TB - NS + 1;
+    constexpr int U = NSTEADY / (TB >= 40 ? 3 : 2);
+    int k = NS - 1;
+#pragma unroll 1
+    for (; k + U <= TB; k += U) {
+      T v[U];
 #pragma unroll
-    for (int i = 0; i < RB; ++i) out[(r + i) * 32] = v[i];
+      for (int u = 0; u < U; ++u) v[u] = (T)in[(k + u) * 32];
+#pragma unroll
+      for (int u = 0; u < U; ++u) out[(k + u - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, v[u], yp, z0, z1);
+    }
+#pragma unroll 1
+    for (; k < TB; ++k) out[(k - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, (T)in[k * 32], yp, z0, z1);
+    WaveDrain<T, G, NS, 1, NS>::run(q, pc, out + (TB - NS + 1) * 32, yp, z0, z1);
+    return;
   }
-  for (; r < rows; ++r) {
+  for (int r = 0; r < rows; ++r) {
     T x = (T)in[r * 32];
 #pragma unroll
     for (int s = 0; s < NS; ++s) {
@@ -111,24 +161,29 @@ __device__ __forceinline__ void pipe_rows(const Cascade& q, const PipeConst& pc,
 
 template <int S, int TB, typename T>
 struct PipeSmem {
-  static constexpr int NX = TB >= 40 ? 2 : 3;                  // TMA ring depth
-  static constexpr int kBsRing = 16;                           // hop-block sums kept (>= nb - 1 + 2 * TB / hop)
+  static constexpr int NX = 2;                                 // TMA ring depth (tile n+1 is in flight while tile n is filtered)
+  static constexpr int kBsRing = 32;                           // hop-block sums kept (>= 2 * TB / hop + nb - 1)
   static constexpr size_t x_bytes = (size_t)NX * TB * 32 * 8;  // f64 input tiles
   static constexpr size_t link_bytes = (size_t)S * 2 * TB * 32 * sizeof(T);
   static constexpr size_t bs_bytes = (size_t)kBsRing * 32 * 8;
-  static constexpr size_t total = 128 + x_bytes + link_bytes + bs_bytes + 64;
+  static constexpr size_t total = x_bytes + link_bytes + bs_bytes + 64;
 };
 
-// One CTA = one (work item, 32-channel group); S warps = S section groups.
-template <typename T, int S, int TB>
-__global__ void __launch_bounds__(32 * S) k_hga_pipe(const __grid_constant__ Cascade q, const __grid_constant__ PipeConst pc,
+// One CTA = one (work item, 32-channel group).  Warps [0, S) are the filter warps (one section group each); warps
+// [S, 2S) are the framing warps: they issue the TMA loads, reduce the y tiles to hop-block power sums and turn closed
+// frames into log / z-score features, so that their latency-bound chains (LDS -> FP64 add chain -> log) overlap with
+// the pipe-bound filter warps instead of extending every step.  HOP = hop size (compile time: 10 or 20).
+template <typename T, int S, int TB, int HOP>
+__global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cascade q, const __grid_constant__ PipeConst pc,
                                                       const __grid_constant__ FusedArgs a, const __grid_constant__ CUtensorMap tmap) {
   constexpr int NS = kMaxSec / S;
-  constexpr int RB = 10;
   using SM = PipeSmem<S, TB, T>;
   constexpr int NX = SM::NX;
-  extern __shared__ unsigned char smem_raw[];
-  unsigned char* base = (unsigned char*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
+  constexpr int NBT = TB / HOP;  // hop blocks per tile
+  static_assert(TB % HOP == 0, "tile must hold whole hop blocks");
+  static_assert(2 * NBT + kMaxBlocksPerFrame - 1 <= SM::kBsRing, "block-sum ring too small");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  unsigned char* base = smem_raw;
   double* xring = (double*)base;                                    // [NX][TB][32]
   T* links = (T*)(base + SM::x_bytes);                              // [S][2][TB][32]; link S-1 is the y tile
   double* bs = (double*)(base + SM::x_bytes + SM::link_bytes);      // [kBsRing][32]
@@ -138,23 +193,9 @@ __global__ void __launch_bounds__(32 * S) k_hga_pipe(const __grid_constant__ Cas
   const int item = blockIdx.x / cg, c0 = (blockIdx.x % cg) * 32;
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const Work wk = a.work[item];
-  const int hop = a.hop, nb = a.nb;
   const int64_t span = wk.t_end - wk.t_begin;
   const int ntiles = (int)((span + TB - 1) / TB);
-  const bool fresh = wk.t_begin == 0;
-  const int c = c0 + lane;
-  const bool zs = a.mu != nullptr;
-  const double mu = (zs && c < a.C) ? a.mu[c] : 0.0;
-  const double inv_sigma = (zs && c < a.C) ? 1.0 / a.sigma[c] : 1.0;
-
-  T z0[NS], z1[NS];
-#pragma unroll
-  for (int s = 0; s < NS; ++s) {
-    // section index g*NS+s is warp-uniform but not compile-time: read the initial state through a small switch-free
-    // constant-bank lookup (once per kernel)
-    z0[s] = fresh ? (T)pc.zu0[g * NS + s] : (T)0;
-    z1[s] = fresh ? (T)pc.zu1[g * NS + s] : (T)0;
-  }
+  const int row_origin = (int)(wk.row0 + wk.t_begin - a.x_row_lo);  // TMA row coordinate of the item's first row
 
   if (threadIdx.x == 0) {
 #pragma unroll
@@ -163,74 +204,122 @@ __global__ void __launch_bounds__(32 * S) k_hga_pipe(const __grid_constant__ Cas
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     for (int i = 0; i < NX - 1 && i < ntiles; ++i) {
       mbar_expect_tx(&full[i], TB * 32 * 8);
-      tma_load_2d(xring + (size_t)i * TB * 32, &tmap, c0, (int)(wk.row0 + wk.t_begin + (int64_t)i * TB - a.x_row_lo), &full[i]);
+      tma_load_2d(xring + (size_t)i * TB * 32, &tmap, c0, row_origin + i * TB, &full[i]);
     }
   }
   __syncthreads();
 
-  const int nbt = TB / hop;  // hop blocks per tile
-  const int64_t blk_begin = wk.t_begin / hop;
-  double* op = a.out + wk.out_row0 * a.ldo + c;
+  long long pr[6] = {0, 0, 0, 0, 0, 0};  // role, tma wait, phase A, phase B, barrier, total
+  const bool prof = a.prof != nullptr;
+  long long tk = prof ? clock64() : 0, tstart = tk;
+#define HGA_TICK(slot)                  \
+  if (prof) {                           \
+    const long long now_ = clock64();   \
+    pr[slot] += now_ - tk;              \
+    tk = now_;                          \
+  }
 
-  for (int n = 0; n < ntiles + S + 1; ++n) {
-    const int tile = n - g;
-    if (tile >= 0 && tile < ntiles) {
-      const int rows = (int)min((int64_t)TB, span - (int64_t)tile * TB);
-      T* out = links + ((size_t)(g * 2 + (tile & 1)) * TB) * 32 + lane;
-      if (g == 0) {
-        const int pre = tile + NX - 1;
-        if (lane == 0 && pre < ntiles) {
+  if (g < S) {
+    // ------------------------------------------------------------------ filter warps
+    const bool fresh = wk.t_begin == 0;
+    T z0[NS], z1[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {  // g * NS + s is warp-uniform: a constant-bank lookup, once per kernel
+      z0[s] = fresh ? (T)pc.zu0[g * NS + s] : (T)0;
+      z1[s] = fresh ? (T)pc.zu1[g * NS + s] : (T)0;
+    }
+    for (int n = 0; n < ntiles + S + 1; ++n) {
+      const int tile = n - g;
+      if (tile >= 0 && tile < ntiles) {
+        const int rows = (int)min((int64_t)TB, span - (int64_t)tile * TB);
+        T* out = links + ((size_t)(g * 2 + (tile & 1)) * TB) * 32 + lane;
+        if (g == 0) {
+          mbar_wait(&full[tile % NX], (tile / NX) & 1);
+          HGA_TICK(1)
+          pipe_rows<T, double, 0, NS, TB>(q, pc, xring + (size_t)(tile % NX) * TB * 32 + lane, out, rows, z0, z1);
+        } else {
+          const T* in = links + ((size_t)((g - 1) * 2 + (tile & 1)) * TB) * 32 + lane;
+          if (S >= 2 && g == 1) pipe_rows<T, T, (S >= 2 ? 1 : 0), NS, TB>(q, pc, in, out, rows, z0, z1);
+          if (S >= 4 && g == 2) pipe_rows<T, T, (S >= 4 ? 2 : 0), NS, TB>(q, pc, in, out, rows, z0, z1);
+          if (S >= 4 && g == 3) pipe_rows<T, T, (S >= 4 ? 3 : 0), NS, TB>(q, pc, in, out, rows, z0, z1);
+        }
+      }
+      HGA_TICK(0)
+      asm volatile("bar.sync 0;" ::: "memory");
+      HGA_TICK(4)
+    }
+  } else {
+    // ------------------------------------------------------------------ framing warps
+    const int w = g - S;
+    const int nb = a.nb;
+    const int c = c0 + lane;
+    const bool zs = a.mu != nullptr;
+    const double mu = (zs && c < a.C) ? a.mu[c] : 0.0;
+    const double inv_sigma = (zs && c < a.C) ? 1.0 / a.sigma[c] : 1.0;
+    const int64_t blk_begin = wk.t_begin / HOP;
+    double* op = a.out + wk.out_row0 * a.ldo + c;
+    for (int n = 0; n < ntiles + S + 1; ++n) {
+      // TMA producer: the slot of tile n + NX - 1 was last read by filter warp 0 in step n - 1
+      if (w == 0 && lane == 0) {
+        const int pre = n + NX - 1;
+        if (pre < ntiles) {
           uint64_t* b = &full[pre % NX];
           mbar_expect_tx(b, TB * 32 * 8);
-          tma_load_2d(xring + (size_t)(pre % NX) * TB * 32, &tmap, c0, (int)(wk.row0 + wk.t_begin + (int64_t)pre * TB - a.x_row_lo), b);
+          tma_load_2d(xring + (size_t)(pre % NX) * TB * 32, &tmap, c0, row_origin + pre * TB, b);
         }
-        mbar_wait(&full[tile % NX], (tile / NX) & 1);
-        pipe_rows<T, double, 0, NS, RB>(q, pc, xring + (size_t)(tile % NX) * TB * 32 + lane, out, rows, z0, z1);
-      } else {
-        const T* in = links + ((size_t)((g - 1) * 2 + (tile & 1)) * TB) * 32 + lane;
-        if (S >= 2 && g == 1) pipe_rows<T, T, (S >= 2 ? 1 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
-        if (S >= 4 && g == 2) pipe_rows<T, T, (S >= 4 ? 2 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
-        if (S >= 4 && g == 3) pipe_rows<T, T, (S >= 4 ? 3 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
-        if (S >= 8 && g == 4) pipe_rows<T, T, (S >= 8 ? 4 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
-        if (S >= 8 && g == 5) pipe_rows<T, T, (S >= 8 ? 5 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
-        if (S >= 8 && g == 6) pipe_rows<T, T, (S >= 8 ? 6 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
-        if (S >= 8 && g == 7) pipe_rows<T, T, (S >= 8 ? 7 : 0), NS, RB>(q, pc, in, out, rows, z0, z1);
       }
-    }
-    // ---- framing, all warps: phase A = hop-block power sums of y tile mA (written by warp S-1 in step n-1);
-    //      phase B = frames closed by the blocks of tile mA-1 (sums written in step n-1).
-    const int mA = n - S, mB = n - S - 1;
-    if (mA >= 0 && mA < ntiles) {
-      const T* yt = links + ((size_t)((S - 1) * 2 + (mA & 1)) * TB) * 32 + lane;
-      const int64_t t0 = wk.t_begin + (int64_t)mA * TB;
-      for (int j = g; j < nbt; j += S) {
-        const int64_t tb = t0 + (int64_t)j * hop;
-        if (tb >= wk.t_acc && tb + hop <= wk.t_end) {
-          double acc = 0.0;
-          for (int i = 0; i < hop; ++i) {
-            const double v = (double)yt[(j * hop + i) * 32];
-            acc = fma(v, v, acc);
+      HGA_TICK(1)
+      // phase A: hop-block power sums of y tile mA (written by filter warp S-1 in step n-1)
+      const int mA = n - S, mB = n - S - 1;
+      if (mA >= 0 && mA < ntiles) {
+        const T* yt = links + ((size_t)((S - 1) * 2 + (mA & 1)) * TB) * 32 + lane;
+        const int64_t t0 = wk.t_begin + (int64_t)mA * TB;
+#pragma unroll
+        for (int j0 = 0; j0 < NBT; j0 += S) {
+          const int j = j0 + w;
+          const int64_t tb = t0 + (int64_t)j * HOP;
+          if (j < NBT && tb >= wk.t_acc && tb + HOP <= wk.t_end) {
+            double v[HOP];
+#pragma unroll
+            for (int i = 0; i < HOP; ++i) v[i] = (double)yt[(j * HOP + i) * 32];
+            double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+            for (int i = 0; i < HOP; i += 2) {
+              acc0 = fma(v[i], v[i], acc0);
+              acc1 = fma(v[i + 1], v[i + 1], acc1);
+            }
+            bs[((blk_begin + (int64_t)mA * NBT + j) & (SM::kBsRing - 1)) * 32 + lane] = acc0 + acc1;
           }
-          bs[((blk_begin + (int64_t)mA * nbt + j) & (SM::kBsRing - 1)) * 32 + lane] = acc;
         }
       }
-    }
-    if (mB >= 0 && mB < ntiles && c < a.C) {
-      const int64_t t0 = wk.t_begin + (int64_t)mB * TB;
-      for (int j = g; j < nbt; j += S) {
-        const int64_t tb = t0 + (int64_t)j * hop;
-        if (tb >= wk.t_acc + (int64_t)(nb - 1) * hop && tb + hop <= wk.t_end) {
-          const int64_t blk = blk_begin + (int64_t)mB * nbt + j;
-          double sum = 0.0;
-          for (int k = nb - 1; k >= 0; --k) sum += bs[((blk - k) & (SM::kBsRing - 1)) * 32 + lane];
-          double f = log(fma(sum, pc.pow_scale, a.eps));
-          if (zs) f = (f - mu) * inv_sigma;
-          op[(blk - (nb - 1)) * a.ldo] = f;
+      HGA_TICK(2)
+      // phase B: frames closed by the blocks of tile mB (their sums were written in step n-1 or earlier)
+      if (mB >= 0 && mB < ntiles && c < a.C) {
+        const int64_t t0 = wk.t_begin + (int64_t)mB * TB;
+#pragma unroll
+        for (int j0 = 0; j0 < NBT; j0 += S) {
+          const int j = j0 + w;
+          const int64_t tb = t0 + (int64_t)j * HOP;
+          if (j < NBT && tb >= wk.t_acc + (int64_t)(nb - 1) * HOP && tb + HOP <= wk.t_end) {
+            const int64_t blk = blk_begin + (int64_t)mB * NBT + j;
+            double sum = 0.0;
+            for (int k = nb - 1; k >= 0; --k) sum += bs[((blk - k) & (SM::kBsRing - 1)) * 32 + lane];
+            double f = log(fma(sum, pc.pow_scale, a.eps));
+            if (zs) f = (f - mu) * inv_sigma;
+            op[(blk - (nb - 1)) * a.ldo] = f;
+          }
         }
       }
+      HGA_TICK(3)
+      asm volatile("bar.sync 0;" ::: "memory");
+      HGA_TICK(4)
     }
-    asm volatile("bar.sync 0;" ::: "memory");
   }
+  if (prof && lane == 0) {
+    pr[5] = clock64() - tstart;
+    for (int i = 0; i < 6; ++i) a.prof[((size_t)blockIdx.x * 8 + g) * 6 + i] = pr[i];
+  }
+#undef HGA_TICK
 }
 
 }  // namespace hga

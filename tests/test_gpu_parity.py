@@ -157,7 +157,7 @@ def test_offline_time_chunked_long(torch):
     assert a <= TOL_F64, (a, r)
 
 
-@pytest.mark.parametrize("variant,S,TB", [("0", "4", "40"), ("1", "4", "40"), ("1", "2", "40"), ("1", "8", "20"), ("1", "4", "20")])
+@pytest.mark.parametrize("variant,S,TB", [("0", "4", "40"), ("1", "4", "40"), ("1", "2", "40")])
 def test_offline_kernel_variants_agree(variant, S, TB, torch, monkeypatch):
     """The thread-sequential and the section-pipelined kernels (every warps-per-item / tile shape) against the oracle:
     ragged segments (partial tiles, lengths that are not hop multiples), C not a multiple of 32, z-score."""
