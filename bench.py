@@ -167,6 +167,38 @@ def run_reference(args):
     }))
 
 
+def stream_latency(fs, C, mu, sigma, device, n_push=10000, warm=500, chunk=10):
+    """p50 / p99 per-packet latency (us) of hga_stream_push_host (H2D of the packet + one kernel + D2H of the frame inside
+    the timed call) and of the reference composition fed the same packets (bounded: 2000 packets)."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    x = np.random.default_rng(20241104).standard_normal(((n_push + warm) * chunk, C))
+    eng = HgaEngine(fs, C, precision="exact", device=device)
+    lat = np.empty(n_push + warm)
+    for i in range(n_push + warm):
+        pkt = x[i * chunk:(i + 1) * chunk]
+        t0 = time.perf_counter()
+        eng.push(pkt, mu, sigma)
+        lat[i] = time.perf_counter() - t0
+    lat = lat[warm:] * 1e6
+    from oracle import build_ref, hga_oracle as O   # cpu-baseline leg: the reference composition on the same packets
+    ref = build_ref.load()
+    oex = O.HighGammaExtractor(fs, C, post_transforms=[O.ZScoreNormalization(mu, sigma)],
+                               log_power=(ref.compute_log_power_features if ref is not None else O.compute_log_power_features_fast))
+    n_ref = 2000
+    rl = np.empty(n_ref)
+    for i in range(n_ref):
+        pkt = x[i * chunk:(i + 1) * chunk]
+        t0 = time.perf_counter()
+        oex.extract_features(pkt)
+        rl[i] = time.perf_counter() - t0
+    rl = rl[200:] * 1e6
+    return {"packet": f"{chunk} x {C} float64", "n": int(n_push), "p50_us": float(np.percentile(lat, 50)),
+            "p99_us": float(np.percentile(lat, 99)), "max_us": float(lat.max()),
+            "path": "hga_stream_push_host: pinned staging, H2D + 1 kernel + D2H per packet, exact arithmetic",
+            "reference_p50_us": float(np.percentile(rl, 50)), "reference_p99_us": float(np.percentile(rl, 99)),
+            "reference_n": int(len(rl))}
+
+
 def workload_name(w):
     fs, C, secs = WORKLOADS[w]
     return f"{w}: {C} ch x {secs} s @ {fs} Hz float64, band-pass+notch cascade, 50ms/10ms log-power, z-score"
@@ -228,6 +260,15 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
+    # dominant-kernel time: CUDA events recorded by the library on the launching stream around the kernel itself
+    eng.set_timing(True)
+    kms = []
+    for _ in range(min(args.steps, 10)):
+        step()
+        kms.append(eng.last_kernel_ms())
+    eng.set_timing(False)
+    kernel_ms = float(np.median(kms))
+    barrier()
     l0 = lib.hga_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
@@ -274,13 +315,49 @@ def run_b200(args):
     except Exception as exc:  # report, do not hide
         e2e = {"value": None, "unit": UNIT, "error": repr(exc)}
 
+    # ---- the other offline precision on the same resident input (reported beside the headline, same timing rules)
+    other = {}
+    for prec in ("f64", "f32"):
+        if prec == args.precision:
+            continue
+        try:
+            e2 = HgaEngine(fs, C, precision=prec, device=local)
+            o2 = torch.empty_like(out)
+            for _ in range(3):
+                e2.extract_offline(x, None, mu, sigma, out=o2)
+            barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(args.steps):
+                e2.extract_offline(x, None, mu, sigma, out=o2)
+            a1.record()
+            barrier()
+            ms2 = a0.elapsed_time(a1) / args.steps
+            if world > 1:
+                t = torch.tensor([ms2], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms2 = float(t.item())
+            other[prec] = {"value": world * C * T / (ms2 / 1e3), "ms_per_step": ms2,
+                           "max_abs_diff_vs_headline": float((o2 - out).abs().max().item()), "warmup_samples": e2.warmup}
+            del e2, o2
+        except Exception as exc:
+            other[prec] = {"error": repr(exc)}
+
+    # ---- streaming (BASELINE config 3): 10-sample x C packets through the host-buffer C-ABI call, carried state
+    stream = None
+    if rank == 0 and world == 1 and not args.no_stream:
+        try:
+            stream = stream_latency(fs, C, mu.cpu().numpy(), sigma.cpu().numpy(), local)
+        except Exception as exc:
+            stream = {"error": repr(exc)}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     hop = eng.hop
     bytes_per = 8.0 + 8.0 / hop
-    achieved = C * T * bytes_per / (ms / 1e3) / 1e9  # per rank: one launch per step
+    achieved = C * T * bytes_per / (kernel_ms / 1e3) / 1e9  # per rank: one launch per step
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         v, kind, sample = reference_rate(fs, C, 60, 1, budget_s=12.0)
@@ -298,8 +375,13 @@ def run_b200(args):
                    "sessions_per_rank": 1, "stats_exchange_ms": stats_ms},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                      "traffic": traffic, "peak_source": peak_src, "bytes_per_channel_sample": bytes_per,
-                     "kernel_ms": ms},
+                     "kernel": "k_hga_pipe (section-pipelined cascade + framing + log + z-score)", "kernel_ms": kernel_ms,
+                     "binding_pipe": "fp64" if args.precision == "f64" else "fma (f32x2)"},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
+        "other_precisions": {k: dict(v, roofline_frac=(C * T * bytes_per / (v["ms_per_step"] / 1e3) / 1e9 / hbm_peak)
+                                      if "ms_per_step" in v else None) for k, v in other.items()},
+        "tolerance": {"f64": "max-abs 1e-9 per feature vs float64 oracle", "f32": "max-abs 1e-4 per feature vs float64 oracle"},
+        "stream_latency": stream,
     }
     print(json.dumps(line))
     if world > 1:
@@ -315,6 +397,7 @@ def main():
     ap.add_argument("--workload", default="k2", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="f64", choices=["f64", "f32", "exact"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-stream", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -173,9 +173,15 @@ static void build_pipe_const(const Cascade& q, int L, PipeConst& pc) {
     G *= q.g[s];
     pc.zu0[s] = q.zi0[s] / G;
     pc.zu1[s] = q.zi1[s] / G;
-    pc.a1f[s] = (float)q.a1[s];
-    pc.a2f[s] = (float)q.a2[s];
-    pc.b1uf[s] = (float)q.b1u[s];
+    auto pack = [](double v) {
+      const float f = (float)v;
+      uint32_t u;
+      memcpy(&u, &f, 4);
+      return ((unsigned long long)u << 32) | u;
+    };
+    pc.na1p[s] = pack(-q.a1[s]);
+    pc.na2p[s] = pack(-q.a2[s]);
+    pc.b1p[s] = pack(q.b1u[s]);
   }
   pc.pow_scale = G * G / (double)L;
 }
@@ -203,7 +209,8 @@ static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs&
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, 64 * S, smem));
     return HGA_OK;
   }
-  const int cg = (a.C + 31) / 32;
+  constexpr int CW = 32 * PipeTraits<T>::CPL;
+  const int cg = (a.C + CW - 1) / CW;
   kern<<<(unsigned)((int64_t)a.n_work * cg), 64 * S, smem, st>>>(q, pc, a, tm);
   LAUNCHED();
   return HGA_OK;
@@ -218,10 +225,11 @@ static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs&
     return pipe_launch_t<T, 4, 40, 10>(q, pc, a, tm, st, occ);
   }
   if (p.S == 2) return pipe_launch_t<T, 2, 40, 20>(q, pc, a, tm, st, occ);
+  if (p.TB == 20) return pipe_launch_t<T, 4, 20, 20>(q, pc, a, tm, st, occ);
   return pipe_launch_t<T, 4, 40, 20>(q, pc, a, tm, st, occ);
 }
 static bool pipe_supported(const Cascade& q, int hop, int nb) {
-  return is_unit_std(q) && (hop == 10 || hop == 20) && nb >= 1 && nb <= 8 && encode_tiled_fn() != nullptr;
+  return is_unit_std(q) && (hop == 10 || hop == 20) && nb == kPipeNB && encode_tiled_fn() != nullptr;
 }
 // x must be 16-byte aligned with an even leading dimension for the TMA descriptor
 static bool pipe_layout_ok(const double* x, int64_t ldx) { return ((uintptr_t)x % 16) == 0 && (ldx % 2) == 0; }
@@ -230,20 +238,21 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
   const cuuint64_t dims[2] = {(cuuint64_t)a.C, (cuuint64_t)(a.x_row_hi - a.x_row_lo)};
   const cuuint64_t strides[1] = {(cuuint64_t)a.ldx * 8};
   const PipeShape p = pipe_shape();
-  const cuuint32_t box[2] = {32, (cuuint32_t)p.TB};
+  const cuuint32_t box[2] = {precision == HGA_PREC_F32 ? 64u : 32u, (cuuint32_t)p.TB};
   const cuuint32_t es[2] = {1, 1};
   void* base = (void*)(a.x + a.x_row_lo * a.ldx);
   const CUresult r = encode_tiled_fn()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(HGA_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   if (getenv("HGA_B200_PROF")) {  // debugging aid: per-warp cycle breakdown, printed to stderr (synchronises)
-    const size_t n_cta = (size_t)a.n_work * ((a.C + 31) / 32), n = n_cta * 8 * 6;
+    const int cw_ = precision == HGA_PREC_F32 ? 64 : 32;
+    const size_t n_cta = (size_t)a.n_work * ((a.C + cw_ - 1) / cw_), n = n_cta * 8 * 6;
     long long* d = nullptr;
     CU(cudaMalloc(&d, n * 8));
     CU(cudaMemset(d, 0, n * 8));
     FusedArgs b = a;
     b.prof = d;
-    int rc = precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, b, b.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, b, b.hop, tm, st, nullptr);
+    int rc = precision == HGA_PREC_F32 ? pipe_dispatch<f32x2>(q, pc, b, b.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, b, b.hop, tm, st, nullptr);
     CU(cudaStreamSynchronize(st));
     std::vector<long long> hbuf(n);
     CU(cudaMemcpy(hbuf.data(), d, n * 8, cudaMemcpyDeviceToHost));
@@ -260,15 +269,16 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
     }
     return rc;
   }
-  return precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, a.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, a.hop, tm, st, nullptr);
+  return precision == HGA_PREC_F32 ? pipe_dispatch<f32x2>(q, pc, a, a.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, a.hop, tm, st, nullptr);
 }
 static int64_t pipe_item_slots(const Cascade& q, const PipeConst& pc, int precision, int hop, int n_sm, int C) {
   int occ = 1;
   FusedArgs a{};
   CUtensorMap tm{};
-  if ((precision == HGA_PREC_F32 ? pipe_dispatch<float>(q, pc, a, hop, tm, nullptr, &occ) : pipe_dispatch<double>(q, pc, a, hop, tm, nullptr, &occ)) != HGA_OK) occ = 1;
+  if ((precision == HGA_PREC_F32 ? pipe_dispatch<f32x2>(q, pc, a, hop, tm, nullptr, &occ) : pipe_dispatch<double>(q, pc, a, hop, tm, nullptr, &occ)) != HGA_OK) occ = 1;
   if (const char* e = getenv("HGA_B200_PIPE_OCC")) occ = std::max(1, std::min(occ, atoi(e)));
-  return std::max<int64_t>(1, (int64_t)n_sm * std::max(1, occ) / ((C + 31) / 32));
+  const int cw = precision == HGA_PREC_F32 ? 64 : 32;
+  return std::max<int64_t>(1, (int64_t)n_sm * std::max(1, occ) / ((C + cw - 1) / cw));
 }
 
 // ------------------------------------------------------------------------------------------------ the handle

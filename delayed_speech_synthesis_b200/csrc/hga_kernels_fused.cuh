@@ -114,7 +114,9 @@ __global__ void __launch_bounds__(128, 3) k_hga_fused_seq(const __grid_constant_
   }
   FrameAcc fa;
   fa.init();
-  if (fresh && a.remainder_in) fa.preload(a.remainder_in + c, a.C, hop, a.nb);
+  // only the item that accumulates from row 0 continues the carried frame buffer; later items that merely START at
+  // row 0 (their warm-up reaches back to it) begin accumulating at t_acc > 0 with an empty ring
+  if (fresh && a.remainder_in && wk.t_acc == 0) fa.preload(a.remainder_in + c, a.C, hop, a.nb);
   const bool zs = a.mu != nullptr;
   const double mu = zs ? a.mu[c] : 0.0, sigma = zs ? a.sigma[c] : 1.0;
   const double* xp = a.x + wk.row0 * a.ldx + c;

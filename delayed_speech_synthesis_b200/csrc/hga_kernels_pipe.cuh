@@ -26,7 +26,7 @@ namespace hga {
 struct PipeConst {  // compile-time-indexable, warp-uniform operands (constant bank)
   double zu0[kMaxSec], zu1[kMaxSec];  // sosfilt_zi divided by the gains in front of each section
   double pow_scale;                   // G^2 / L
-  float a1f[kMaxSec], a2f[kMaxSec], b1uf[kMaxSec];
+  unsigned long long na1p[kMaxSec], na2p[kMaxSec], b1p[kMaxSec];  // (-a1,-a1), (-a2,-a2), (b1u,b1u) as float32 pairs
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -59,17 +59,62 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       : "memory");
 }
 
-template <typename T> struct PipeCoef;
-template <> struct PipeCoef<double> {
-  static __device__ __forceinline__ double a1(const Cascade& q, const PipeConst&, int s) { return q.a1[s]; }
-  static __device__ __forceinline__ double a2(const Cascade& q, const PipeConst&, int s) { return q.a2[s]; }
+// Two float32 lanes in one 64-bit register (fma.rn.f32x2 / add.rn.f32x2, SASS FFMA2 / FADD2): one lane of a warp filters
+// TWO channels (c and c + 32) per instruction, which halves the issue slots of the float32 cascade.
+struct f32x2 {
+  unsigned long long v;
+};
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
+__device__ __forceinline__ f32x2 operator+(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+using ::fma;  // keep the scalar overloads visible next to the packed one
+__device__ __forceinline__ f32x2 fma(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+
+// Per-arithmetic traits: channels per lane, coefficient operands (warp-uniform constant-bank reads; a1 / a2 are stored
+// negated for the packed type, negated through the operand modifier otherwise), conversions at the tile boundaries.
+template <typename T> struct PipeTraits;
+template <> struct PipeTraits<double> {
+  static constexpr int CPL = 1;
+  static __device__ __forceinline__ double na1(const Cascade& q, const PipeConst&, int s) { return -q.a1[s]; }
+  static __device__ __forceinline__ double na2(const Cascade& q, const PipeConst&, int s) { return -q.a2[s]; }
   static __device__ __forceinline__ double b1(const Cascade& q, const PipeConst&, int s) { return q.b1u[s]; }
+  static __device__ __forceinline__ double zero() { return 0.0; }
+  static __device__ __forceinline__ double splat(double v) { return v; }
+  static __device__ __forceinline__ double load_x(const double* p) { return p[0]; }
+  static __device__ __forceinline__ void split(double y, double (&o)[1]) { o[0] = y; }
 };
-template <> struct PipeCoef<float> {
-  static __device__ __forceinline__ float a1(const Cascade&, const PipeConst& p, int s) { return p.a1f[s]; }
-  static __device__ __forceinline__ float a2(const Cascade&, const PipeConst& p, int s) { return p.a2f[s]; }
-  static __device__ __forceinline__ float b1(const Cascade&, const PipeConst& p, int s) { return p.b1uf[s]; }
+template <> struct PipeTraits<f32x2> {
+  static constexpr int CPL = 2;
+  static __device__ __forceinline__ f32x2 na1(const Cascade&, const PipeConst& p, int s) { return f32x2{p.na1p[s]}; }
+  static __device__ __forceinline__ f32x2 na2(const Cascade&, const PipeConst& p, int s) { return f32x2{p.na2p[s]}; }
+  static __device__ __forceinline__ f32x2 b1(const Cascade&, const PipeConst& p, int s) { return f32x2{p.b1p[s]}; }
+  static __device__ __forceinline__ f32x2 zero() { return f32x2{0ull}; }
+  static __device__ __forceinline__ f32x2 splat(double v) { return pack2((float)v, (float)v); }
+  static __device__ __forceinline__ f32x2 load_x(const double* p) { return pack2((float)p[0], (float)p[32]); }
+  static __device__ __forceinline__ void split(f32x2 y, double (&o)[2]) {
+    float a, b;
+    unpack2(y, a, b);
+    o[0] = (double)a;
+    o[1] = (double)b;
+  }
 };
+// tile readers: x tiles hold 32 * CPL doubles per row, links hold 32 T per row
+template <typename T>
+__device__ __forceinline__ T pipe_load(const double* in, int r) { return PipeTraits<T>::load_x(in + r * 32 * PipeTraits<T>::CPL); }
+template <typename T>
+__device__ __forceinline__ T pipe_load(const f32x2* in, int r) { return in[r * 32]; }
 
 // One wavefront step: section s in [LO, HI] consumes the output its predecessor produced in the PREVIOUS step (section 0
 // consumes x0), so the NS section updates of a step are mutually independent and the four instruction groups below
@@ -77,7 +122,7 @@ template <> struct PipeCoef<float> {
 // latency at one issue per 2 cycles is covered by a single warp when NS >= 4.  Returns the output of section NS-1.
 template <typename T, int G, int NS, int LO, int HI>
 __device__ __forceinline__ T wave_step(const Cascade& q, const PipeConst& pc, T x0, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
-  using K = PipeCoef<T>;
+  using K = PipeTraits<T>;
   T xin[NS], yn[NS], t[NS];
 #pragma unroll
   for (int s = LO; s <= HI; ++s) xin[s] = s == 0 ? x0 : yp[s - 1];
@@ -86,9 +131,9 @@ __device__ __forceinline__ T wave_step(const Cascade& q, const PipeConst& pc, T 
 #pragma unroll
   for (int s = LO; s <= HI; ++s) t[s] = fma(K::b1(q, pc, G * NS + s), xin[s], z1[s]);
 #pragma unroll
-  for (int s = LO; s <= HI; ++s) z0[s] = fma(-K::a1(q, pc, G * NS + s), yn[s], t[s]);
+  for (int s = LO; s <= HI; ++s) z0[s] = fma(K::na1(q, pc, G * NS + s), yn[s], t[s]);
 #pragma unroll
-  for (int s = LO; s <= HI; ++s) z1[s] = fma(-K::a2(q, pc, G * NS + s), yn[s], xin[s]);
+  for (int s = LO; s <= HI; ++s) z1[s] = fma(K::na2(q, pc, G * NS + s), yn[s], xin[s]);
 #pragma unroll
   for (int s = LO; s <= HI; ++s) yp[s] = yn[s];
   return yn[NS - 1];
@@ -107,7 +152,7 @@ struct WaveFill<T, G, NS, K1, K1> {
 template <typename T, int G, int NS, int J, int J1>  // epilogue steps: sections J..NS-1 active, one output each
 struct WaveDrain {
   static __device__ __forceinline__ void run(const Cascade& q, const PipeConst& pc, T* o, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
-    o[(J - 1) * 32] = wave_step<T, G, NS, J, NS - 1>(q, pc, (T)0, yp, z0, z1);
+    o[(J - 1) * 32] = wave_step<T, G, NS, J, NS - 1>(q, pc, PipeTraits<T>::zero(), yp, z0, z1);
     WaveDrain<T, G, NS, J + 1, J1>::run(q, pc, o, yp, z0, z1);
   }
 };
@@ -121,76 +166,137 @@ struct WaveDrain<T, G, NS, J1, J1> {
 template <typename T, typename TIN, int G, int NS, int TB>
 __device__ __forceinline__ void pipe_rows(const Cascade& q, const PipeConst& pc, const TIN* __restrict__ in, T* __restrict__ out,
                                           int rows, T (&z0)[NS], T (&z1)[NS]) {
-  using K = PipeCoef<T>;
+  using K = PipeTraits<T>;
   if (rows == TB) {
     T yp[NS];
     {
       T v[NS > 1 ? NS - 1 : 1];
 #pragma unroll
-      for (int i = 0; i < NS - 1; ++i) v[i] = (T)in[i * 32];
+      for (int i = 0; i < NS - 1; ++i) v[i] = pipe_load<T>(in, i);
       WaveFill<T, G, NS, 0, NS - 1>::run(q, pc, v, yp, z0, z1);
     }
+    // steady state: all NS sections busy.  Small loop body (2 * U wavefront steps ~ 2.5 KB of SASS) so that the loop
+    // stays in the sub-partition's L0 instruction cache (a 12-step body made the float32x2 variant fetch-bound:
+    // ncu stall_no_instruction 1.1 per issue), with the next U input rows loaded while the current U are filtered.
+    constexpr int U = 4;
     constexpr int NSTEADY = TB - NS + 1;
-    constexpr int U = NSTEADY / (TB >= 40 ? 3 : 2);
+    constexpr int NPAIR = NSTEADY / (2 * U);
     int k = NS - 1;
+    T va[U], vb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) va[u] = pipe_load<T>(in, k + u);
 #pragma unroll 1
-    for (; k + U <= TB; k += U) {
-      T v[U];
+    for (int it = 0; it < NPAIR; ++it, k += 2 * U) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) v[u] = (T)in[(k + u) * 32];
+      for (int u = 0; u < U; ++u) vb[u] = pipe_load<T>(in, k + U + u);
 #pragma unroll
-      for (int u = 0; u < U; ++u) out[(k + u - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, v[u], yp, z0, z1);
+      for (int u = 0; u < U; ++u) out[(k + u - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, va[u], yp, z0, z1);
+      if (it + 1 < NPAIR || NSTEADY - NPAIR * 2 * U >= U) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) va[u] = pipe_load<T>(in, k + 2 * U + u);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) out[(k + U + u - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, vb[u], yp, z0, z1);
     }
-#pragma unroll 1
-    for (; k < TB; ++k) out[(k - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, (T)in[k * 32], yp, z0, z1);
+    if (NSTEADY - NPAIR * 2 * U >= U) {  // compile-time: one more batch of U, already in va
+#pragma unroll
+      for (int u = 0; u < U; ++u) out[(k + u - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, va[u], yp, z0, z1);
+      k += U;
+    }
+#pragma unroll
+    for (int r = 0; r < NSTEADY % U; ++r, ++k)
+      out[(k - (NS - 1)) * 32] = wave_step<T, G, NS, 0, NS - 1>(q, pc, pipe_load<T>(in, k), yp, z0, z1);
     WaveDrain<T, G, NS, 1, NS>::run(q, pc, out + (TB - NS + 1) * 32, yp, z0, z1);
     return;
   }
   for (int r = 0; r < rows; ++r) {
-    T x = (T)in[r * 32];
+    T x = pipe_load<T>(in, r);
 #pragma unroll
     for (int s = 0; s < NS; ++s) {
       const T y = x + z0[s];
-      z0[s] = fma(-K::a1(q, pc, G * NS + s), y, fma(K::b1(q, pc, G * NS + s), x, z1[s]));
-      z1[s] = fma(-K::a2(q, pc, G * NS + s), y, x);
+      z0[s] = fma(K::na1(q, pc, G * NS + s), y, fma(K::b1(q, pc, G * NS + s), x, z1[s]));
+      z1[s] = fma(K::na2(q, pc, G * NS + s), y, x);
       x = y;
     }
     out[r * 32] = x;
   }
 }
 
+// Branch-free natural log for finite x > 0 (here x >= eps = 0.01): x = m * 2^e with m in [sqrt(1/2), sqrt(2)),
+// log m = 2 atanh(s), s = (m - 1) / (m + 1), odd series to s^23 (|s| <= 0.1716), reciprocal by two Newton steps on
+// rcp.approx, e * ln2 in two parts.  <= 2 ulp against glibc over [1e-2, 1e15] (tools/check_fast_log.py).  No special
+// cases means several logs of one thread interleave, which the framing warps rely on.
+__device__ __forceinline__ double fast_log(double x) {
+  const long long bits = __double_as_longlong(x);
+  int e = (int)((bits >> 52) & 0x7ff) - 1023;
+  double m = __longlong_as_double((bits & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);  // [1, 2)
+  const bool big = m > 1.4142135623730951;
+  m = big ? m * 0.5 : m;
+  e = big ? e + 1 : e;
+  const double d = m + 1.0;
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  r = fma(r, fma(-d, r, 1.0), r);
+  r = fma(r, fma(-d, r, 1.0), r);
+  const double num = m - 1.0;
+  double sv = num * r;
+  sv = fma(fma(-d, sv, num), r, sv);  // one correction step: s = num / d to within an ulp
+  const double z = sv * sv;
+  double qv = 1.0 / 23.0;
+  qv = fma(z, qv, 1.0 / 21.0);
+  qv = fma(z, qv, 1.0 / 19.0);
+  qv = fma(z, qv, 1.0 / 17.0);
+  qv = fma(z, qv, 1.0 / 15.0);
+  qv = fma(z, qv, 1.0 / 13.0);
+  qv = fma(z, qv, 1.0 / 11.0);
+  qv = fma(z, qv, 1.0 / 9.0);
+  qv = fma(z, qv, 1.0 / 7.0);
+  qv = fma(z, qv, 1.0 / 5.0);
+  qv = fma(z, qv, 1.0 / 3.0);
+  qv *= z;
+  const double ed = (double)e, s2 = sv + sv;
+  return fma(ed, 0x1.62e42fee00000p-1, s2) + fma(s2, qv, ed * 0x1.a39ef35793c76p-33);
+}
+
+constexpr int kFrameBatch = 4;  // tiles per log / z-score / store batch of the framing warps
+constexpr int kPipeNB = 5;      // hop blocks per frame the pipe kernel is built for (L = 5 * hop at 1 and 2 kHz)
+
 template <int S, int TB, typename T>
 struct PipeSmem {
-  static constexpr int NX = 2;                                 // TMA ring depth (tile n+1 is in flight while tile n is filtered)
-  static constexpr int kBsRing = 32;                           // hop-block sums kept (>= 2 * TB / hop + nb - 1)
-  static constexpr size_t x_bytes = (size_t)NX * TB * 32 * 8;  // f64 input tiles
+  static constexpr int CPL = PipeTraits<T>::CPL;
+  static constexpr int NX = 2;        // TMA ring depth (tile n+1 is in flight while tile n is filtered)
+  static constexpr int kBsRing = TB >= 40 ? 32 : 16;  // hop-block sums kept (>= (kFrameBatch + 1) * TB / hop + nb - 1)
+  static constexpr size_t x_bytes = (size_t)NX * TB * 32 * CPL * 8;  // f64 input tiles
   static constexpr size_t link_bytes = (size_t)S * 2 * TB * 32 * sizeof(T);
-  static constexpr size_t bs_bytes = (size_t)kBsRing * 32 * 8;
+  static constexpr size_t bs_bytes = (size_t)kBsRing * 32 * CPL * 8;
   static constexpr size_t total = x_bytes + link_bytes + bs_bytes + 64;
 };
 
-// One CTA = one (work item, 32-channel group).  Warps [0, S) are the filter warps (one section group each); warps
-// [S, 2S) are the framing warps: they issue the TMA loads, reduce the y tiles to hop-block power sums and turn closed
-// frames into log / z-score features, so that their latency-bound chains (LDS -> FP64 add chain -> log) overlap with
-// the pipe-bound filter warps instead of extending every step.  HOP = hop size (compile time: 10 or 20).
+// One CTA = one (work item, group of 32 * CPL channels).  Warps [0, S) are the filter warps (one section group each);
+// warps [S, 2S) are the framing warps: they issue the TMA loads, reduce the y tiles to hop-block power sums and turn
+// closed frames into log / z-score features, so that their latency-bound chains (LDS -> FP64 add chain -> log) overlap
+// with the pipe-bound filter warps instead of extending every step.  HOP = hop size (compile time: 10 or 20).
 template <typename T, int S, int TB, int HOP>
-__global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cascade q, const __grid_constant__ PipeConst pc,
+__global__ void __launch_bounds__(64 * S, TB >= 40 ? 1 : 3) k_hga_pipe(const __grid_constant__ Cascade q, const __grid_constant__ PipeConst pc,
                                                       const __grid_constant__ FusedArgs a, const __grid_constant__ CUtensorMap tmap) {
   constexpr int NS = kMaxSec / S;
   using SM = PipeSmem<S, TB, T>;
+  using TR = PipeTraits<T>;
+  constexpr int CPL = TR::CPL, CW = 32 * CPL;  // channels per lane / per CTA
   constexpr int NX = SM::NX;
   constexpr int NBT = TB / HOP;  // hop blocks per tile
+  constexpr uint32_t kTileBytes = TB * CW * 8;
   static_assert(TB % HOP == 0, "tile must hold whole hop blocks");
-  static_assert(2 * NBT + kMaxBlocksPerFrame - 1 <= SM::kBsRing, "block-sum ring too small");
+  static_assert((kFrameBatch + 1) * NBT + kPipeNB - 1 <= SM::kBsRing, "block-sum ring too small");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char* base = smem_raw;
-  double* xring = (double*)base;                                    // [NX][TB][32]
+  double* xring = (double*)base;                                    // [NX][TB][CW]
   T* links = (T*)(base + SM::x_bytes);                              // [S][2][TB][32]; link S-1 is the y tile
-  double* bs = (double*)(base + SM::x_bytes + SM::link_bytes);      // [kBsRing][32]
+  double* bs = (double*)(base + SM::x_bytes + SM::link_bytes);      // [kBsRing][CW]
   uint64_t* full = (uint64_t*)(base + SM::x_bytes + SM::link_bytes + SM::bs_bytes);  // [NX]
 
-  const int cg = (a.C + 31) / 32;
-  const int item = blockIdx.x / cg, c0 = (blockIdx.x % cg) * 32;
+  const int cg = (a.C + CW - 1) / CW;
+  const int item = blockIdx.x / cg, c0 = (blockIdx.x % cg) * CW;
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const Work wk = a.work[item];
   const int64_t span = wk.t_end - wk.t_begin;
@@ -203,8 +309,8 @@ __global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cas
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     for (int i = 0; i < NX - 1 && i < ntiles; ++i) {
-      mbar_expect_tx(&full[i], TB * 32 * 8);
-      tma_load_2d(xring + (size_t)i * TB * 32, &tmap, c0, row_origin + i * TB, &full[i]);
+      mbar_expect_tx(&full[i], kTileBytes);
+      tma_load_2d(xring + (size_t)i * TB * CW, &tmap, c0, row_origin + i * TB, &full[i]);
     }
   }
   __syncthreads();
@@ -225,8 +331,8 @@ __global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cas
     T z0[NS], z1[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s) {  // g * NS + s is warp-uniform: a constant-bank lookup, once per kernel
-      z0[s] = fresh ? (T)pc.zu0[g * NS + s] : (T)0;
-      z1[s] = fresh ? (T)pc.zu1[g * NS + s] : (T)0;
+      z0[s] = fresh ? TR::splat(pc.zu0[g * NS + s]) : TR::zero();
+      z1[s] = fresh ? TR::splat(pc.zu1[g * NS + s]) : TR::zero();
     }
     for (int n = 0; n < ntiles + S + 1; ++n) {
       const int tile = n - g;
@@ -236,7 +342,7 @@ __global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cas
         if (g == 0) {
           mbar_wait(&full[tile % NX], (tile / NX) & 1);
           HGA_TICK(1)
-          pipe_rows<T, double, 0, NS, TB>(q, pc, xring + (size_t)(tile % NX) * TB * 32 + lane, out, rows, z0, z1);
+          pipe_rows<T, double, 0, NS, TB>(q, pc, xring + (size_t)(tile % NX) * TB * CW + lane, out, rows, z0, z1);
         } else {
           const T* in = links + ((size_t)((g - 1) * 2 + (tile & 1)) * TB) * 32 + lane;
           if (S >= 2 && g == 1) pipe_rows<T, T, (S >= 2 ? 1 : 0), NS, TB>(q, pc, in, out, rows, z0, z1);
@@ -251,21 +357,24 @@ __global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cas
   } else {
     // ------------------------------------------------------------------ framing warps
     const int w = g - S;
-    const int nb = a.nb;
-    const int c = c0 + lane;
     const bool zs = a.mu != nullptr;
-    const double mu = (zs && c < a.C) ? a.mu[c] : 0.0;
-    const double inv_sigma = (zs && c < a.C) ? 1.0 / a.sigma[c] : 1.0;
+    double mu[CPL], inv_sigma[CPL];
+#pragma unroll
+    for (int p = 0; p < CPL; ++p) {
+      const int c = c0 + lane + 32 * p;
+      mu[p] = (zs && c < a.C) ? a.mu[c] : 0.0;
+      inv_sigma[p] = (zs && c < a.C) ? 1.0 / a.sigma[c] : 1.0;
+    }
     const int64_t blk_begin = wk.t_begin / HOP;
-    double* op = a.out + wk.out_row0 * a.ldo + c;
+    double* op = a.out + wk.out_row0 * a.ldo + c0 + lane;
     for (int n = 0; n < ntiles + S + 1; ++n) {
       // TMA producer: the slot of tile n + NX - 1 was last read by filter warp 0 in step n - 1
       if (w == 0 && lane == 0) {
         const int pre = n + NX - 1;
         if (pre < ntiles) {
           uint64_t* b = &full[pre % NX];
-          mbar_expect_tx(b, TB * 32 * 8);
-          tma_load_2d(xring + (size_t)(pre % NX) * TB * 32, &tmap, c0, row_origin + pre * TB, b);
+          mbar_expect_tx(b, kTileBytes);
+          tma_load_2d(xring + (size_t)(pre % NX) * TB * CW, &tmap, c0, row_origin + pre * TB, b);
         }
       }
       HGA_TICK(1)
@@ -279,34 +388,62 @@ __global__ void __launch_bounds__(64 * S) k_hga_pipe(const __grid_constant__ Cas
           const int j = j0 + w;
           const int64_t tb = t0 + (int64_t)j * HOP;
           if (j < NBT && tb >= wk.t_acc && tb + HOP <= wk.t_end) {
-            double v[HOP];
+            T v[HOP];
 #pragma unroll
-            for (int i = 0; i < HOP; ++i) v[i] = (double)yt[(j * HOP + i) * 32];
-            double acc0 = 0.0, acc1 = 0.0;
+            for (int i = 0; i < HOP; ++i) v[i] = yt[(j * HOP + i) * 32];
+            double acc0[CPL], acc1[CPL];
+#pragma unroll
+            for (int p = 0; p < CPL; ++p) acc0[p] = acc1[p] = 0.0;
 #pragma unroll
             for (int i = 0; i < HOP; i += 2) {
-              acc0 = fma(v[i], v[i], acc0);
-              acc1 = fma(v[i + 1], v[i + 1], acc1);
+              double u0[CPL], u1[CPL];
+              TR::split(v[i], u0);
+              TR::split(v[i + 1], u1);
+#pragma unroll
+              for (int p = 0; p < CPL; ++p) {
+                acc0[p] = fma(u0[p], u0[p], acc0[p]);
+                acc1[p] = fma(u1[p], u1[p], acc1[p]);
+              }
             }
-            bs[((blk_begin + (int64_t)mA * NBT + j) & (SM::kBsRing - 1)) * 32 + lane] = acc0 + acc1;
+#pragma unroll
+            for (int p = 0; p < CPL; ++p)
+              bs[((blk_begin + (int64_t)mA * NBT + j) & (SM::kBsRing - 1)) * CW + lane + 32 * p] = acc0[p] + acc1[p];
           }
         }
       }
       HGA_TICK(2)
-      // phase B: frames closed by the blocks of tile mB (their sums were written in step n-1 or earlier)
-      if (mB >= 0 && mB < ntiles && c < a.C) {
-        const int64_t t0 = wk.t_begin + (int64_t)mB * TB;
+      // phase B, every kFrameBatch tiles: log / z-score / store of the frames closed by the blocks of tiles [mB0, mB]
+      // (their sums were written in step n-1 or earlier); PER * CPL independent logs in flight per thread
+      if (mB >= 0 && mB < ntiles && (mB % kFrameBatch == kFrameBatch - 1 || mB == ntiles - 1)) {
+        const int mB0 = mB - mB % kFrameBatch;
+        const int nblk = (mB - mB0 + 1) * NBT;
+        const int64_t blk0 = blk_begin + (int64_t)mB0 * NBT;
+        constexpr int PER = (kFrameBatch * NBT + S - 1) / S;
+        double sum[PER][CPL];
+        bool ok[PER];
 #pragma unroll
-        for (int j0 = 0; j0 < NBT; j0 += S) {
-          const int j = j0 + w;
-          const int64_t tb = t0 + (int64_t)j * HOP;
-          if (j < NBT && tb >= wk.t_acc + (int64_t)(nb - 1) * HOP && tb + HOP <= wk.t_end) {
-            const int64_t blk = blk_begin + (int64_t)mB * NBT + j;
-            double sum = 0.0;
-            for (int k = nb - 1; k >= 0; --k) sum += bs[((blk - k) & (SM::kBsRing - 1)) * 32 + lane];
-            double f = log(fma(sum, pc.pow_scale, a.eps));
-            if (zs) f = (f - mu) * inv_sigma;
-            op[(blk - (nb - 1)) * a.ldo] = f;
+        for (int u = 0; u < PER; ++u) {
+          const int jb = u * S + w;
+          const int64_t blk = blk0 + jb, tb = blk * HOP;
+          ok[u] = jb < nblk && tb >= wk.t_acc + (int64_t)(kPipeNB - 1) * HOP && tb + HOP <= wk.t_end;
+#pragma unroll
+          for (int p = 0; p < CPL; ++p) {
+            double v[kPipeNB];
+#pragma unroll
+            for (int k = 0; k < kPipeNB; ++k) v[k] = bs[((blk - (kPipeNB - 1) + k) & (SM::kBsRing - 1)) * CW + lane + 32 * p];
+            double sacc = v[0];
+#pragma unroll
+            for (int k = 1; k < kPipeNB; ++k) sacc += v[k];  // oldest block first, like the sequential kernel
+            sum[u][p] = ok[u] ? sacc : 1.0;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+#pragma unroll
+          for (int p = 0; p < CPL; ++p) {
+            double f = fast_log(fma(sum[u][p], pc.pow_scale, a.eps));
+            if (zs) f = (f - mu[p]) * inv_sigma[p];
+            if (ok[u] && c0 + lane + 32 * p < a.C) op[(blk0 + u * S + w - (kPipeNB - 1)) * a.ldo + 32 * p] = f;
           }
         }
       }
