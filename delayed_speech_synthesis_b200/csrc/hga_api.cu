@@ -15,7 +15,7 @@
 #include "hga_common.cuh"
 #include "hga_kernels_exact.cuh"
 #include "hga_kernels_fused.cuh"
-#include "hga_kernels_pipe.cuh"
+#include "hga_kernels_pipe2.cuh"
 
 using namespace hga;
 
@@ -185,15 +185,38 @@ static void build_pipe_const(const Cascade& q, int L, PipeConst& pc) {
   }
   pc.pow_scale = G * G / (double)L;
 }
+// log table of tab_log (hga_kernels_pipe2.cuh): entry i = {rc, -log(rc)} with rc = double(1 / (1 + (i + 1/2) / 128))
+static int upload_log_table() {
+  double tab[2 * kLogTabN];
+  for (int i = 0; i < kLogTabN; ++i) {
+    const double rc = (double)(1.0L / (1.0L + ((long double)i + 0.5L) / (long double)kLogTabN));
+    tab[2 * i] = rc;
+    tab[2 * i + 1] = (double)(-logl((long double)rc));
+  }
+  CU(cudaMemcpyToSymbol(g_logtab, tab, sizeof tab));
+  return HGA_OK;
+}
 struct PipeShape {
-  int S, TB;
+  int ver, S, TB;
 };
-static PipeShape pipe_shape() {
-  PipeShape p{4, 40};
+// Default: k_hga_pipe2 with 4 filter warps x 4 sections and 40-row tiles, one CTA per SM (measured best for both
+// precisions on K2, profiles/r01_pipe2_sweep.txt).  HGA_B200_PIPE_V=1 selects the first-generation kernel (k_hga_pipe,
+// S in {2, 4}); HGA_B200_PIPE_S / HGA_B200_PIPE_TB pick the other compiled shapes (A/B runs).
+static PipeShape pipe_shape(bool f32 = false) {
+  (void)f32;
+  PipeShape p{2, 4, 40};
+  if (const char* e = getenv("HGA_B200_PIPE_V")) p.ver = atoi(e) == 1 ? 1 : 2;
+  if (p.ver == 1) { p.S = 4; p.TB = 40; }
   if (const char* e = getenv("HGA_B200_PIPE_S")) p.S = atoi(e);
   if (const char* e = getenv("HGA_B200_PIPE_TB")) p.TB = atoi(e);
-  if (p.S != 2 && p.S != 4) p.S = 4;
-  if (p.TB != 20 || p.S != 4) p.TB = 40;
+  if (p.ver == 1) {
+    if (p.S != 2 && p.S != 4) p.S = 4;
+    if (p.TB != 20 || p.S != 4) p.TB = 40;
+  } else {
+    if (p.S != 4 && p.S != 8) p.S = 4;
+    if (p.S == 8) p.TB = 20;
+    else if (p.TB != 20 && p.TB != 40) p.TB = 40;
+  }
   return p;
 }
 template <typename T, int S, int TB, int HOP>
@@ -215,10 +238,42 @@ static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs&
   LAUNCHED();
   return HGA_OK;
 }
+constexpr int kPipe2NF = 4;  // framing warps of k_hga_pipe2
+template <typename T, int S, int TB, int HOP>
+static int pipe2_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
+  // S == 4: one section group per SM sub-partition -> per-group code with constant-bank coefficients; S == 8: shared code.
+  constexpr bool kPerG = S == 4;
+  auto kern = k_hga_pipe2<T, S, TB, HOP, kPipe2NF, kPerG>;
+  const int smem = (int)Pipe2Smem<S, TB, T>::total, threads = 32 * (S + kPipe2NF);
+  static bool attr_done = false;
+  if (!attr_done) {
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_done = true;
+  }
+  if (occ) {
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, threads, smem));
+    return HGA_OK;
+  }
+  constexpr int CW = 32 * PipeTraits<T>::CPL;
+  const int cg = (a.C + CW - 1) / CW;
+  kern<<<(unsigned)((int64_t)a.n_work * cg), threads, smem, st>>>(q, pc, a, tm);
+  LAUNCHED();
+  return HGA_OK;
+}
 // occ != nullptr: only query the resident CTAs per SM of the variant that would be launched.
 template <typename T>
 static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs& a, int hop, const CUtensorMap& tm, cudaStream_t st, int* occ) {
-  const PipeShape p = pipe_shape();
+  const PipeShape p = pipe_shape(PipeTraits<T>::CPL == 2);
+  if (p.ver == 2) {
+    if (hop == 10) {
+      if (p.S == 8) return pipe2_launch_t<T, 8, 20, 10>(q, pc, a, tm, st, occ);
+      if (p.TB == 20) return pipe2_launch_t<T, 4, 20, 10>(q, pc, a, tm, st, occ);
+      return pipe2_launch_t<T, 4, 40, 10>(q, pc, a, tm, st, occ);
+    }
+    if (p.S == 8) return pipe2_launch_t<T, 8, 20, 20>(q, pc, a, tm, st, occ);
+    if (p.TB == 20) return pipe2_launch_t<T, 4, 20, 20>(q, pc, a, tm, st, occ);
+    return pipe2_launch_t<T, 4, 40, 20>(q, pc, a, tm, st, occ);
+  }
   if (hop == 10) {
     if (p.S == 2) return pipe_launch_t<T, 2, 40, 10>(q, pc, a, tm, st, occ);
     if (p.TB == 20) return pipe_launch_t<T, 4, 20, 10>(q, pc, a, tm, st, occ);
@@ -237,7 +292,7 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
   CUtensorMap tm;
   const cuuint64_t dims[2] = {(cuuint64_t)a.C, (cuuint64_t)(a.x_row_hi - a.x_row_lo)};
   const cuuint64_t strides[1] = {(cuuint64_t)a.ldx * 8};
-  const PipeShape p = pipe_shape();
+  const PipeShape p = pipe_shape(precision == HGA_PREC_F32);
   const cuuint32_t box[2] = {precision == HGA_PREC_F32 ? 64u : 32u, (cuuint32_t)p.TB};
   const cuuint32_t es[2] = {1, 1};
   void* base = (void*)(a.x + a.x_row_lo * a.ldx);
@@ -246,7 +301,8 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
   if (r != CUDA_SUCCESS) return fail(HGA_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   if (getenv("HGA_B200_PROF")) {  // debugging aid: per-warp cycle breakdown, printed to stderr (synchronises)
     const int cw_ = precision == HGA_PREC_F32 ? 64 : 32;
-    const size_t n_cta = (size_t)a.n_work * ((a.C + cw_ - 1) / cw_), n = n_cta * 8 * 6;
+    const int wstride = p.ver == 2 ? 16 : 8;
+    const size_t n_cta = (size_t)a.n_work * ((a.C + cw_ - 1) / cw_), n = n_cta * wstride * 6;
     long long* d = nullptr;
     CU(cudaMalloc(&d, n * 8));
     CU(cudaMemset(d, 0, n * 8));
@@ -257,11 +313,11 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
     std::vector<long long> hbuf(n);
     CU(cudaMemcpy(hbuf.data(), d, n * 8, cudaMemcpyDeviceToHost));
     cudaFree(d);
-    const char* names[6] = {"role", "tma_wait", "phaseA", "phaseB", "barrier", "total"};
-    for (int g = 0; g < 8; ++g) {
+    const char* names[6] = {"role", "wait_in", "phaseA", "phaseB", "wait_out", "total"};
+    for (int g = 0; g < wstride; ++g) {
       double acc[6] = {0};
       for (size_t cta = 0; cta < n_cta; ++cta)
-        for (int i = 0; i < 6; ++i) acc[i] += (double)hbuf[(cta * 8 + g) * 6 + i];
+        for (int i = 0; i < 6; ++i) acc[i] += (double)hbuf[(cta * wstride + g) * 6 + i];
       if (acc[5] == 0) continue;
       fprintf(stderr, "[hga prof] warp %d:", g);
       for (int i = 0; i < 6; ++i) fprintf(stderr, " %s=%.0f", names[i], acc[i] / n_cta);
@@ -346,6 +402,7 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   int rc = build_cascade(h->q, cfg->sos_bp, cfg->n_sections_bp, cfg->zi_bp, cfg->sos_notch, cfg->n_sections_notch, cfg->zi_notch);
   if (rc) { delete h; return rc; }
   build_pipe_const(h->q, cfg->frame_len, h->pc);
+  if ((rc = upload_log_table())) { delete h; return rc; }
   cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, cfg->device);
   h->overlap = cfg->frame_len - cfg->hop;
   h->nb = (cfg->frame_len % cfg->hop == 0 && cfg->frame_len / cfg->hop <= kMaxBlocksPerFrame) ? cfg->frame_len / cfg->hop : 0;

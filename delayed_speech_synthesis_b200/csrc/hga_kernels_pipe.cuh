@@ -94,6 +94,7 @@ template <> struct PipeTraits<double> {
   static __device__ __forceinline__ double splat(double v) { return v; }
   static __device__ __forceinline__ double load_x(const double* p) { return p[0]; }
   static __device__ __forceinline__ void split(double y, double (&o)[1]) { o[0] = y; }
+  static __device__ __forceinline__ double load_part(const double* p, int) { return p[0]; }
 };
 template <> struct PipeTraits<f32x2> {
   static constexpr int CPL = 2;
@@ -109,6 +110,8 @@ template <> struct PipeTraits<f32x2> {
     o[0] = (double)a;
     o[1] = (double)b;
   }
+  // channel half `part` (0: lane, 1: lane + 32) of a packed pair in shared memory, widened
+  static __device__ __forceinline__ double load_part(const f32x2* p, int part) { return (double)reinterpret_cast<const float*>(p)[part]; }
 };
 // tile readers: x tiles hold 32 * CPL doubles per row, links hold 32 T per row
 template <typename T>
