@@ -366,6 +366,8 @@ def run_b200(args):
     tp = ROOT / "profiles" / "traffic.json"
     if tp.exists():
         traffic = json.loads(tp.read_text()).get(args.workload)
+        if isinstance(traffic, dict):
+            traffic = traffic.get(args.precision)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
@@ -375,7 +377,7 @@ def run_b200(args):
                    "sessions_per_rank": 1, "stats_exchange_ms": stats_ms},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                      "traffic": traffic, "peak_source": peak_src, "bytes_per_channel_sample": bytes_per,
-                     "kernel": "k_hga_pipe (section-pipelined cascade + framing + log + z-score)", "kernel_ms": kernel_ms,
+                     "kernel": "k_hga_pipe2 (section-pipelined cascade + framing + log + z-score)", "kernel_ms": kernel_ms,
                      "binding_pipe": "fp64" if args.precision == "f64" else "fma (f32x2)"},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
         "other_precisions": {k: dict(v, roofline_frac=(C * T * bytes_per / (v["ms_per_step"] / 1e3) / 1e9 / hbm_peak)
@@ -391,7 +393,7 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="k2", choices=sorted(WORKLOADS))
