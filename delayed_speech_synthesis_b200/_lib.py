@@ -57,6 +57,10 @@ SIGNATURES = {
     "hga_stats_accumulate": (C.c_int, [_i32, _vp, _i64, _i32, _i64, _vp, _vp]),
     "hga_stats_merge": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _vp]),
     "hga_stats_finalize": (C.c_int, [_i32, _vp, _i32, _vp, _vp, _vp]),
+    "hga_chanmap_create": (C.c_int, [_i32, _i32, _i32, _pi32, _pi32, _vp, _vp, _i32, _pi32, _pi32, C.POINTER(_vp)]),
+    "hga_chanmap_destroy": (C.c_int, [_vp]),
+    "hga_chanmap_apply": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64, _vp]),
+    "hga_chanmap_apply_host": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64]),
     "hga_launch_count": (_i64, []),
     "hga_set_timing": (C.c_int, [_vp, _i32]),
     "hga_last_kernel_ms": (_dbl, [_vp]),

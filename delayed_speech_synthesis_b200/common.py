@@ -1,7 +1,10 @@
-"""Host-side mirror of the one `local/common.py` class on the HGA path."""
+"""Host-side mirror of the `local/common.py` classes on and next to the HGA path: `ZScoreNormalization` here, the
+channel-axis transforms (`ChannelSelection`, `CommonAverageReferencing`, `BadChannelCorrection`) in transforms.py."""
 from __future__ import annotations
 
 import numpy as np
+
+from .transforms import BadChannelCorrection, ChannelSelection, CommonAverageReferencing  # noqa: F401  (local/common.py:16-58,220-365)
 
 
 class ZScoreNormalization:

@@ -16,6 +16,7 @@
 #include "hga_kernels_exact.cuh"
 #include "hga_kernels_fused.cuh"
 #include "hga_kernels_pipe2.cuh"
+#include "hga_kernels_pre.cuh"
 
 using namespace hga;
 
@@ -916,6 +917,102 @@ extern "C" int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t
   CU(cudaSetDevice(device));
   k_stats_finalize<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(acc_dev, C, mu_dev, sigma_dev);
   LAUNCHED();
+  return HGA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ channel maps
+// Gather / common-average-reference / bad-channel patch along the channel axis (hga_kernels_pre.cuh).
+struct hga_chanmap {
+  int device = 0, c_in = 0, c_out = 0, n_groups = 0, n_sm = 0;
+  DevBuf tab;  // sel | grp | gptr | gidx (int32) followed by alpha | beta (double)
+  const int32_t *sel = nullptr, *grp = nullptr, *gptr = nullptr, *gidx = nullptr;
+  const double *alpha = nullptr, *beta = nullptr;
+  DevBuf xdev, odev;  // staging of the host-buffer variant
+};
+
+extern "C" int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, const int32_t* sel, const int32_t* grp, const double* alpha,
+                                  const double* beta, int32_t n_groups, const int32_t* gptr, const int32_t* gidx, hga_chanmap** out) {
+  if (!out) return fail(HGA_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (!sel || !grp || !alpha || !beta || (n_groups > 0 && (!gptr || !gidx))) return fail(HGA_ERR_INVALID, "null argument");
+  if (c_in < 1 || c_out < 1 || n_groups < 0 || n_groups > kChanMapMaxGroups) return fail(HGA_ERR_INVALID, "bad shape: c_in=%d c_out=%d groups=%d (max %d)", c_in, c_out, n_groups, kChanMapMaxGroups);
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  if (device < 0 || device >= hga_device_count()) return fail(HGA_ERR_INVALID, "bad device %d", device);
+  const int n_idx = n_groups > 0 ? gptr[n_groups] : 0;
+  for (int j = 0; j < c_out; ++j) {
+    if (sel[j] < -1 || sel[j] >= c_in) return fail(HGA_ERR_INVALID, "sel[%d] = %d outside [0, %d)", j, sel[j], c_in);
+    if (grp[j] < -1 || grp[j] >= n_groups) return fail(HGA_ERR_INVALID, "grp[%d] = %d outside [0, %d)", j, grp[j], n_groups);
+  }
+  for (int g = 0; g < n_groups; ++g)
+    if (gptr[g + 1] <= gptr[g]) return fail(HGA_ERR_INVALID, "group %d is empty", g);
+  for (int k = 0; k < n_idx; ++k)
+    if (gidx[k] < 0 || gidx[k] >= c_in) return fail(HGA_ERR_INVALID, "group column %d outside [0, %d)", gidx[k], c_in);
+  CU(cudaSetDevice(device));
+  hga_chanmap* m = new hga_chanmap();
+  m->device = device; m->c_in = c_in; m->c_out = c_out; m->n_groups = n_groups;
+  cudaDeviceGetAttribute(&m->n_sm, cudaDevAttrMultiProcessorCount, device);
+  const size_t n_i32 = (size_t)2 * c_out + (n_groups + 1) + n_idx, off_d = (n_i32 * 4 + 15) / 16 * 16;
+  std::vector<unsigned char> hbuf(off_d + (size_t)2 * c_out * 8, 0);
+  int32_t* hi = reinterpret_cast<int32_t*>(hbuf.data());
+  memcpy(hi, sel, (size_t)c_out * 4);
+  memcpy(hi + c_out, grp, (size_t)c_out * 4);
+  if (n_groups > 0) {
+    memcpy(hi + 2 * c_out, gptr, (size_t)(n_groups + 1) * 4);
+    memcpy(hi + 2 * c_out + n_groups + 1, gidx, (size_t)n_idx * 4);
+  }
+  double* hd = reinterpret_cast<double*>(hbuf.data() + off_d);
+  memcpy(hd, alpha, (size_t)c_out * 8);
+  memcpy(hd + c_out, beta, (size_t)c_out * 8);
+  int rc = m->tab.reserve(hbuf.size());
+  if (rc) { delete m; return rc; }
+  if (cudaMemcpy(m->tab.p, hbuf.data(), hbuf.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+    m->tab.release();
+    delete m;
+    return fail(HGA_ERR_CUDA, "upload of the channel-map tables failed: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  const int32_t* di = m->tab.as<int32_t>();
+  m->sel = di; m->grp = di + c_out; m->gptr = di + 2 * c_out; m->gidx = di + 2 * c_out + n_groups + 1;
+  m->alpha = reinterpret_cast<const double*>(static_cast<unsigned char*>(m->tab.p) + off_d);
+  m->beta = m->alpha + c_out;
+  *out = m;
+  return HGA_OK;
+}
+extern "C" int hga_chanmap_destroy(hga_chanmap* m) {
+  if (!m) return HGA_OK;
+  cudaSetDevice(m->device);
+  m->tab.release(); m->xdev.release(); m->odev.release();
+  delete m;
+  return HGA_OK;
+}
+extern "C" int hga_chanmap_apply(hga_chanmap* m, const double* x_dev, int64_t T, int64_t ldx, double* out_dev, int64_t ldo, void* stream) {
+  if (!m || !x_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (T < 0 || ldx < m->c_in || ldo < m->c_out) return fail(HGA_ERR_INVALID, "bad shape: T=%lld ldx=%lld ldo=%lld", (long long)T, (long long)ldx, (long long)ldo);
+  if (T == 0) return HGA_OK;
+  CU(cudaSetDevice(m->device));
+  ChanMapArgs a{x_dev, ldx, T, m->c_in, m->c_out, m->n_groups, m->sel, m->grp, m->alpha, m->beta, m->gptr, m->gidx, out_dev, ldo};
+  const size_t smem = (size_t)kChanMapWarps * (m->c_in + kChanMapMaxGroups) * 8;
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    CU(cudaFuncSetAttribute(k_chanmap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(smem, 1)));
+  const int64_t need = (T + kChanMapWarps - 1) / kChanMapWarps;
+  const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)m->n_sm * per_sm));
+  k_chanmap<<<grid, 32 * kChanMapWarps, smem, (cudaStream_t)stream>>>(a);
+  LAUNCHED();
+  return HGA_OK;
+}
+extern "C" int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int64_t T, int64_t ldx, double* out_host, int64_t ldo) {
+  if (!m || !x_host || !out_host) return fail(HGA_ERR_INVALID, "null argument");
+  if (T < 0 || ldx < m->c_in || ldo < m->c_out) return fail(HGA_ERR_INVALID, "bad shape");
+  if (T == 0) return HGA_OK;
+  CU(cudaSetDevice(m->device));
+  int rc;
+  if ((rc = m->xdev.reserve((size_t)T * m->c_in * 8)) || (rc = m->odev.reserve((size_t)T * m->c_out * 8))) return rc;
+  CU(cudaMemcpy2D(m->xdev.p, (size_t)m->c_in * 8, x_host, (size_t)ldx * 8, (size_t)m->c_in * 8, (size_t)T, cudaMemcpyHostToDevice));
+  if ((rc = hga_chanmap_apply(m, m->xdev.as<double>(), T, m->c_in, m->odev.as<double>(), m->c_out, nullptr))) return rc;
+  CU(cudaMemcpy2D(out_host, (size_t)ldo * 8, m->odev.p, (size_t)m->c_out * 8, (size_t)m->c_out * 8, (size_t)T, cudaMemcpyDeviceToHost));
   return HGA_OK;
 }
 

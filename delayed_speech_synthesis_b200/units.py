@@ -13,7 +13,7 @@ from typing import AsyncGenerator, Callable, List, Optional
 
 import numpy as np
 
-from . import filters
+from . import filters, transforms
 from .common import ZScoreNormalization
 from .engine import HgaEngine, _torch
 from .ezmsg_compat import TimeSeriesMessage, ez
@@ -61,10 +61,19 @@ class HighGammaExtractor:
         self.post_transform = post_transforms
 
         # A ZScoreNormalization that is the ONLY post-transform is folded into the feature kernel
-        # (decode_online.py:94-95,109); any other chain is applied as the reference does, in order.
+        # (decode_online.py:94-95,109).  Chains of column selections / common average referencing / bad-channel
+        # correction (prepare_corpus.py:152-169, decode_online.py:66-82) are folded into one channel-map kernel each
+        # (transforms.fold); any other chain is applied as the reference does, by calling the user's callables in order.
         self._fused_zscore = None
+        self._pre_list = list(pre_transforms) if pre_transforms is not None else None
+        self._pre_map = None          # (input width, transforms.ChannelMap or None), built on the first call
+        self._post_map = None
         if post_transforms is not None and len(post_transforms) == 1 and _is_zscore(post_transforms[0]):
             self._fused_zscore = post_transforms[0]
+        elif post_transforms:
+            spec = transforms.fold(post_transforms, nb_electrodes)
+            if spec is not None and spec.c_out == nb_electrodes:
+                self._post_map = spec
         if self.pre_transform is not None:
             self.pre_transform = self._compose_functions(*pre_transforms)          # :115-116
         if self.post_transform is not None:
@@ -108,9 +117,30 @@ class HighGammaExtractor:
         order = (iir_params or {}).get('order', 8)
         return {"sos": filters.create_filter_sos(sr, l_freq, h_freq, order), "order": order, "ftype": "butter"}
 
+    def _apply_pre(self, data):
+        """pre_transforms (:147-148): one channel-map kernel when the chain folds, else the callables themselves."""
+        torch = _torch()
+        width = int(data.shape[1]) if getattr(data, "ndim", 0) == 2 else -1
+        if width > 0 and (self._pre_map is None or self._pre_map[0] != width):
+            spec = transforms.fold(self._pre_list, width)
+            ok = spec is not None and spec.c_out == self.nb_electrodes
+            self._pre_map = (width, transforms.ChannelMap(spec, self._engine.device) if ok else None)
+        cmap = self._pre_map[1] if self._pre_map is not None and width > 0 else None
+        if cmap is None:
+            return self.pre_transform(data)
+        if not isinstance(data, torch.Tensor):
+            data = np.ascontiguousarray(data, dtype=np.float64)
+            if data.shape[0] * data.shape[1] >= (1 << 16):      # large blocks stay on the device for the extraction
+                data = torch.from_numpy(data).cuda(self._engine.device)
+                return ("numpy", cmap.apply(data))
+        return cmap.apply(data)
+
     def extract_features(self, data):                                              # :145-161
+        as_numpy = False
         if self.pre_transform is not None:
-            data = self.pre_transform(data)
+            data = self._apply_pre(data)
+            if isinstance(data, tuple):
+                as_numpy, data = True, data[1]
         mu = sigma = None
         if self._fused_zscore is not None:
             mu, sigma = self._fused_zscore.channel_means, self._fused_zscore.channel_stds
@@ -120,8 +150,14 @@ class HighGammaExtractor:
             if data.dtype != np.float64:   # scipy.signal.sosfilt upcasts (float32 wire data becomes float64, :81)
                 data = data.astype(np.float64)
         data = self._engine.push(data, mu, sigma)
-        if self.post_transform is not None and self._fused_zscore is None:
+        if self._post_map is not None:
+            if not isinstance(self._post_map, transforms.ChannelMap):
+                self._post_map = transforms.ChannelMap(self._post_map, self._engine.device)
+            data = self._post_map.apply(data)
+        elif self.post_transform is not None and self._fused_zscore is None:
             data = self.post_transform(data)
+        if as_numpy and isinstance(data, torch.Tensor):
+            data = data.cpu().numpy()
         return data
 
 

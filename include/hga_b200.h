@@ -159,6 +159,24 @@ int hga_stats_merge(int32_t device, double* acc_a_dev, const double* acc_b_dev, 
 int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t C, double* mu_dev, double* sigma_dev,
                        void* stream);
 
+/* ---- channel-axis transforms either side of the path -------------------------------------- */
+/* One row-wise map  out[t, j] = alpha[j] * x[t, sel[j]] + beta[j] * mean_{c in group grp[j]} x[t, c]  covers
+ *   - SelectElectrodesFromBothGrids / SelectElectrodesOverSpeechAreas.__call__ (local/common.py:31-32,54-55): alpha 1, beta 0;
+ *   - CommonAverageReferencing.__call__ (local/common.py:336-343): alpha 1, beta -1, group = the grid's computation mask;
+ *   - BadChannelCorrection.__call__ (local/common.py:279-284): alpha 0, beta 1, group = the bad channel's neighbours;
+ *   - and gather -> CAR -> gather chains (prepare_corpus.py:152-160, decode_online.py:69-82) folded by the host into
+ *     raw-column indices.  sel[j] = -1 / grp[j] = -1 drop the respective term.  Groups are CSR: columns
+ *     gidx[gptr[g] .. gptr[g+1]) (raw input columns), at most 32 groups.  All table arguments are HOST arrays, copied
+ *     at creation.  In place (out == x, ldo == ldx) is allowed. */
+typedef struct hga_chanmap hga_chanmap;
+int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, const int32_t* sel, const int32_t* grp,
+                       const double* alpha, const double* beta, int32_t n_groups, const int32_t* gptr,
+                       const int32_t* gidx, hga_chanmap** out);
+int hga_chanmap_destroy(hga_chanmap* m);
+int hga_chanmap_apply(hga_chanmap* m, const double* x_dev, int64_t T, int64_t ldx, double* out_dev, int64_t ldo,
+                      void* stream);
+int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int64_t T, int64_t ldx, double* out_host, int64_t ldo);
+
 /* ---- introspection for bench.py / tests ------------------------------------------------------------------------- */
 /* Kernel launches issued through this library by the calling process since load (all handles). */
 int64_t hga_launch_count(void);

@@ -304,3 +304,60 @@ def synthetic_ecog(T: int, C: int, fs: int = 1000, kind: str = "white", seed: in
         t = np.arange(T)[:, None] / fs
         return np.ascontiguousarray(pink + 20.0 * np.sin(2 * np.pi * 60 * t) + 5.0 * np.sin(2 * np.pi * 120 * t + 0.3))
     raise ValueError(kind)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Channel-axis transforms either side of the path: numpy restatements used by the tests to
+# check the channel-map kernel.  Pinned against the reference's own classes, executed from /root/reference/local/common.py
+# by tests/golden/make_golden.py (tests/golden/transforms.npz).
+# ----------------------------------------------------------------------------------------------------------------------
+def select_columns(data: np.ndarray, mapping: Sequence[int]) -> np.ndarray:
+    """SelectElectrodesFromBothGrids / SelectElectrodesOverSpeechAreas.__call__ (local/common.py:31-32, 54-55)."""
+    return data[:, np.asarray(mapping)]
+
+
+def car_masks(exclude_channels: Sequence[int], grids: Sequence[np.ndarray], layout: np.ndarray):
+    """CommonAverageReferencing.__init__ (local/common.py:313-334): per grid, where to apply and where to average."""
+    layout = np.asarray(layout)
+    appl = [np.isin(layout, g) for g in grids]
+    comp = []
+    for g, a in zip(grids, appl):
+        c = a.copy()
+        for ch in exclude_channels:
+            if ch in g:
+                c[np.argmax(layout == ch)] = False
+        comp.append(c)
+    return appl, comp
+
+
+def common_average_reference(data: np.ndarray, appl: Sequence[np.ndarray], comp: Sequence[np.ndarray]) -> np.ndarray:
+    """CommonAverageReferencing.__call__ (local/common.py:336-343): means come from the input, per time sample."""
+    out = data.copy()
+    for a, c in zip(appl, comp):
+        out[:, a] = out[:, a] - np.mean(data[:, c], axis=1)[:, None]
+    return out
+
+
+def bad_channel_patches(bad_channels: Sequence[int], grids: Sequence[np.ndarray], layout: np.ndarray):
+    """BadChannelCorrection.__init__ (local/common.py:224-246,263-277): (column of the bad channel, columns of its
+    non-bad 8-neighbours on the same grid, in row-major grid order)."""
+    layout = np.asarray(layout)
+    patches = []
+    for ch in bad_channels:
+        grid = next(np.asarray(g) for g in grids if ch in g)
+        good = ~np.isin(grid, list(bad_channels))
+        (r,), (c,) = np.where(grid == ch)
+        near = np.zeros(grid.shape, dtype=bool)
+        near[max(r - 1, 0):r + 2, max(c - 1, 0):c + 2] = True
+        near[r, c] = False
+        neigh = grid[near & good]
+        patches.append((np.where(layout == ch)[0], np.concatenate([np.where(layout == n)[0] for n in neigh])))
+    return patches
+
+
+def bad_channel_correction(data: np.ndarray, patches) -> np.ndarray:
+    """BadChannelCorrection.__call__ (local/common.py:279-284)."""
+    out = data.copy()
+    for loc, neigh in patches:
+        out[:, loc] = np.mean(data[:, neigh], axis=1).reshape((len(data), -1))
+    return out

@@ -9,7 +9,9 @@ Pieces executed:
     when a returned slice is released, SURVEY.md §8c — so every returned object is kept and the child leaves via
     os._exit);
   * scipy.signal.sosfilt / sosfilt_zi / iirfilter (the third-party code the reference calls, local/units.py:124-152);
-  * the composition of local/units.py:145-161 written out literally with those pieces.
+  * the composition of local/units.py:145-161 written out literally with those pieces;
+  * the reference's channel-transform classes (local/common.py), cut out of its AST and executed unmodified
+    (`python tests/golden/make_golden.py transforms` regenerates only transforms.npz).
 """
 from __future__ import annotations
 
@@ -53,7 +55,53 @@ def framebuffer_golden():
         subprocess.run([sys.executable, "-c", code], check=True)
 
 
+def reference_transform_classes():
+    """The reference's own channel-transform classes, executed from where they lie: /root/reference/local/common.py cannot
+    be imported here (h5py, sklearn imports at its top), so the five class definitions are cut out of its AST and
+    executed unmodified in a namespace that holds what they use (numpy, scipy.ndimage.binary_dilation, typing.List)."""
+    import ast
+    from typing import List
+    from scipy.ndimage import binary_dilation
+    src = Path("/root/reference/local/common.py").read_text()
+    want = ["SelectElectrodesFromBothGrids", "SelectElectrodesOverSpeechAreas", "BadChannelCorrection", "CommonAverageReferencing",
+            "ZScoreNormalization"]
+    ns = {"np": np, "List": List, "binary_dilation": binary_dilation}
+    for node in ast.parse(src).body:
+        if isinstance(node, ast.ClassDef) and node.name in want:
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "/root/reference/local/common.py", "exec"), ns)
+    return {k: ns[k] for k in want}
+
+
+def transforms_golden():
+    """prepare_corpus.py:147-175 and decode_online.py:64-82 wiring, on seeded data (tests/golden/transforms.npz)."""
+    R = reference_transform_classes()
+    rng = np.random.Generator(np.random.Philox(key=[20241104, 7]))
+    x = rng.standard_normal((97, 128)) * 30 + 20 * np.sin(2 * np.pi * 60 * np.arange(97) / 1000)[:, None]
+    speech_grid = np.flip(np.arange(64, dtype=np.int16).reshape((8, 8)) + 1, axis=0)
+    motor_grid = np.flip(np.arange(64, dtype=np.int16).reshape((8, 8)) + 65, axis=0)
+    layout = np.arange(128) + 1
+    both, speech = R["SelectElectrodesFromBothGrids"](), R["SelectElectrodesOverSpeechAreas"]()
+    car = R["CommonAverageReferencing"](exclude_channels=[19, 38, 48, 52], grids=[speech_grid, motor_grid], layout=layout)
+    bcc = R["BadChannelCorrection"](bad_channels=[19, 38, 48, 52, 1, 64, 100], grids=[speech_grid, motor_grid], layout=layout)
+    a = both(x)
+    b = car(a)
+    c = speech(b)
+    f = rng.standard_normal((61, 128)) * 0.4 + 3.0            # stands for (F, C) features
+    out = {"x": x, "both_mapping": np.asarray(both.grid_mapping), "speech_mapping": np.asarray(speech.speech_grid_mapping),
+           "after_both": a, "after_car": b, "after_speech": c, "exclude": np.array([19, 38, 48, 52]),
+           "car_appl": np.array(car.selection_masks_application), "car_comp": np.array(car.selection_masks_computation),
+           "speech_grid": speech_grid, "motor_grid": motor_grid, "layout": layout,
+           "bad": np.array([19, 38, 48, 52, 1, 64, 100]), "f": f, "after_bcc": bcc(f),
+           "bcc_loc": np.array([int(p[0][0]) for p in bcc.patches]),
+           "bcc_neigh": np.array([np.pad(p[1], (0, 8 - len(p[1])), constant_values=-1) for p in bcc.patches])}
+    np.savez(HERE / "transforms.npz", **out)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "transforms":
+        transforms_golden()
+        print("golden written: transforms.npz")
+        return
     from scipy.signal import iirfilter, sosfilt, sosfilt_zi
     from oracle import build_ref
 
@@ -107,6 +155,7 @@ def main():
     np.savez(HERE / "pipeline.npz", x=x, offline=off, mu=mu, sigma=sd, offline_z=(off - mu) / sd,
              stream=np.concatenate(frames), stream_hg_state=hs, stream_fh_state=fh)
     framebuffer_golden()
+    transforms_golden()
     print("golden written:", sorted(p.name for p in HERE.glob("*.npz")))
 
 
