@@ -186,6 +186,67 @@ static void build_pipe_const(const Cascade& q, int L, PipeConst& pc) {
   }
   pc.pow_scale = G * G / (double)L;
 }
+// Operands of k_hga_pipe2 (hga_kernels_pipe2.cuh, "section forms").  form56: the band-pass numerators are re-paired into
+// [1, 0, -1] sections (possible when its sections are n x [1, 2, 1] and n x [1, -2, 1], which is what scipy designs) and
+// the sections are interleaved so that every filter warp of the kernel gets the same mix: with NS sections per warp,
+// NS/2 band-pass (A) sections followed by NS/2 notch (U) sections.  Otherwise (or HGA_B200_FORM=64): all sections in
+// the U form, in the caller's order.  Section order is free because the cascade is LTI and always starts from zero state.
+static bool can_form56(const Cascade& q) {
+  if (!is_unit_std(q)) return false;
+  int plus = 0, minus = 0;
+  for (int s = 0; s < q.ns_a; ++s) {
+    if (std::fabs(q.b1u[s] - 2.0) <= 1e-13) ++plus;
+    else if (std::fabs(q.b1u[s] + 2.0) <= 1e-13) ++minus;
+    else return false;
+  }
+  if (const char* e = getenv("HGA_B200_FORM")) if (atoi(e) == 64) return false;
+  return plus == minus;
+}
+static void build_pipe2_const(const Cascade& q, int L, int NS, PipeConst& pc) {
+  build_pipe_const(q, L, pc);
+  const bool f56 = can_form56(q);
+  auto pack = [](double v) {
+    const float f = (float)v;
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    return ((unsigned long long)u << 32) | u;
+  };
+  pc.amask = 0;
+  for (int i = 0; i < q.ns; ++i) {
+    int src = i;
+    bool A = false;
+    if (f56) {  // slot i of warp i / NS: first half A sections, second half U sections
+      const int g = i / NS, k = i % NS, half = NS / 2;
+      A = k < half;
+      src = A ? g * half + k : q.ns_a + g * half + (k - half);
+    }
+    pc.c1d[i] = A ? q.a1[src] : -q.a1[src];
+    pc.c2d[i] = A ? q.a2[src] : -q.a2[src];
+    pc.cbd[i] = A ? 0.0 : q.b1u[src];
+    pc.na1p[i] = pack(pc.c1d[i]);
+    pc.na2p[i] = pack(pc.c2d[i]);
+    pc.b1p[i] = pack(pc.cbd[i]);
+    if (A) pc.amask |= 1u << i;
+  }
+}
+// Zero-input response of the caller's initial state (sosfilt_zi of both filters, local/units.py:128-132) through the
+// caller's cascade, exact DF2T order, divided by the gain product: what k_hga_pipe2 adds to the rows of a fresh item.
+static std::vector<double> zero_input_response(const Cascade& q, int n) {
+  std::vector<double> r((size_t)n), z0(q.zi0, q.zi0 + kMaxSec), z1(q.zi1, q.zi1 + kMaxSec);
+  double G = 1.0;
+  for (int s = 0; s < q.ns; ++s) G *= q.g[s];
+  for (int t = 0; t < n; ++t) {
+    double x = 0.0;
+    for (int s = 0; s < q.ns; ++s) {
+      const double y = q.b0[s] * x + z0[s];
+      z0[s] = (q.b1[s] * x - q.a1[s] * y) + z1[s];
+      z1[s] = q.b2[s] * x - q.a2[s] * y;
+      x = y;
+    }
+    r[t] = x / G;
+  }
+  return r;
+}
 // log table of tab_log (hga_kernels_pipe2.cuh): entry i = {rc, -log(rc)} with rc = double(1 / (1 + (i + 1/2) / 128))
 static int upload_log_table() {
   double tab[2 * kLogTabN];
@@ -239,13 +300,18 @@ static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs&
   LAUNCHED();
   return HGA_OK;
 }
-constexpr int kPipe2NF = 4;  // framing warps of k_hga_pipe2
-template <typename T, int S, int TB, int HOP>
-static int pipe2_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
+// framing warps of k_hga_pipe2: 4 (one per SM sub-partition) or 8 (S = 4, TB = 40 only; HGA_B200_PIPE_NF)
+static int pipe2_nf(bool f32) {
+  int nf = f32 ? 8 : 4;
+  if (const char* e = getenv("HGA_B200_PIPE_NF")) nf = atoi(e) == 8 ? 8 : 4;
+  return nf;
+}
+template <typename T, int S, int TB, int HOP, unsigned AM, int kPipe2NF = 4>
+static int pipe2_launch_am(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
   // S == 4: one section group per SM sub-partition -> per-group code with constant-bank coefficients; S == 8: shared code.
   constexpr bool kPerG = S == 4;
-  auto kern = k_hga_pipe2<T, S, TB, HOP, kPipe2NF, kPerG>;
-  const int smem = (int)Pipe2Smem<S, TB, T>::total, threads = 32 * (S + kPipe2NF);
+  auto kern = k_hga_pipe2<T, S, TB, HOP, kPipe2NF, kPerG, AM>;
+  const int smem = (int)Pipe2Smem<S, TB, T>::total, threads = 32 * (S + kPipe2NF + 1);
   static bool attr_done = false;
   if (!attr_done) {
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -260,6 +326,15 @@ static int pipe2_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs
   kern<<<(unsigned)((int64_t)a.n_work * cg), threads, smem, st>>>(q, pc, a, tm);
   LAUNCHED();
   return HGA_OK;
+}
+template <typename T, int S, int TB, int HOP>
+static int pipe2_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
+  constexpr int NS = kMaxSec / S;
+  constexpr unsigned kHalf = (1u << (NS / 2)) - 1u;  // form56: the first NS/2 sections of every warp are A sections
+  if (S == 4 && TB == 40 && pc.amask != 0 && pipe2_nf(PipeTraits<T>::CPL == 2) == 8)
+    return pipe2_launch_am<T, S, TB, HOP, kHalf, (S == 4 && TB == 40 ? 8 : 4)>(q, pc, a, tm, st, occ);
+  if (pc.amask != 0) return pipe2_launch_am<T, S, TB, HOP, kHalf>(q, pc, a, tm, st, occ);
+  return pipe2_launch_am<T, S, TB, HOP, 0u>(q, pc, a, tm, st, occ);
 }
 // occ != nullptr: only query the resident CTAs per SM of the variant that would be launched.
 template <typename T>
@@ -289,7 +364,18 @@ static bool pipe_supported(const Cascade& q, int hop, int nb) {
 }
 // x must be 16-byte aligned with an even leading dimension for the TMA descriptor
 static bool pipe_layout_ok(const double* x, int64_t ldx) { return ((uintptr_t)x % 16) == 0 && (ldx % 2) == 0; }
-static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, const FusedArgs& a, cudaStream_t st) {
+struct PipeOperands {  // what the handle keeps for the pipe kernels
+  PipeConst pc;    // first-generation kernel (k_hga_pipe): caller's sections and initial state
+  PipeConst pc2;   // k_hga_pipe2: its own section order / forms, zero initial state
+  const double* zir = nullptr;  // device, n_zir rows
+  int n_zir = 0;
+};
+static int launch_pipe(const Cascade& q, const PipeOperands& po, int precision, const FusedArgs& a_in, cudaStream_t st) {
+  const bool v2 = pipe_shape().ver == 2;
+  const PipeConst& pc = v2 ? po.pc2 : po.pc;
+  FusedArgs a = a_in;
+  a.zir = po.zir;
+  a.n_zir = po.n_zir;
   CUtensorMap tm;
   const cuuint64_t dims[2] = {(cuuint64_t)a.C, (cuuint64_t)(a.x_row_hi - a.x_row_lo)};
   const cuuint64_t strides[1] = {(cuuint64_t)a.ldx * 8};
@@ -328,7 +414,8 @@ static int launch_pipe(const Cascade& q, const PipeConst& pc, int precision, con
   }
   return precision == HGA_PREC_F32 ? pipe_dispatch<f32x2>(q, pc, a, a.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, a.hop, tm, st, nullptr);
 }
-static int64_t pipe_item_slots(const Cascade& q, const PipeConst& pc, int precision, int hop, int n_sm, int C) {
+static int64_t pipe_item_slots(const Cascade& q, const PipeOperands& po, int precision, int hop, int n_sm, int C) {
+  const PipeConst& pc = pipe_shape().ver == 2 ? po.pc2 : po.pc;
   int occ = 1;
   FusedArgs a{};
   CUtensorMap tm{};
@@ -342,7 +429,8 @@ static int64_t pipe_item_slots(const Cascade& q, const PipeConst& pc, int precis
 struct hga_handle {
   hga_config cfg;
   Cascade q;
-  PipeConst pc;
+  PipeOperands po;
+  DevBuf zir;
   int n_sm = 0;
   int warmup = 0;
   int overlap = 0;   // L - hop
@@ -402,7 +490,8 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   h->cfg = *cfg;
   int rc = build_cascade(h->q, cfg->sos_bp, cfg->n_sections_bp, cfg->zi_bp, cfg->sos_notch, cfg->n_sections_notch, cfg->zi_notch);
   if (rc) { delete h; return rc; }
-  build_pipe_const(h->q, cfg->frame_len, h->pc);
+  build_pipe_const(h->q, cfg->frame_len, h->po.pc);
+  build_pipe2_const(h->q, cfg->frame_len, kMaxSec / pipe_shape().S, h->po.pc2);
   if ((rc = upload_log_table())) { delete h; return rc; }
   cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, cfg->device);
   h->overlap = cfg->frame_len - cfg->hop;
@@ -416,6 +505,15 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   }
   h->warmup = std::max(h->warmup, h->overlap);
   h->warmup = (h->warmup + cfg->hop - 1) / cfg->hop * cfg->hop;
+  if (h->q.ns == kMaxSec) {  // k_hga_pipe2 candidates: zero-input response of the initial state, down to 1e-15 of its start
+    int n = r > 0 ? (int)std::min(1e6, std::ceil(std::log(1e-15) / std::log(r))) : 1;
+    n = (std::max(n, 1) + cfg->hop - 1) / cfg->hop * cfg->hop;
+    const std::vector<double> zr = zero_input_response(h->q, n);
+    if ((rc = h->zir.reserve((size_t)n * 8))) { delete h; return rc; }
+    CU(cudaMemcpy(h->zir.p, zr.data(), (size_t)n * 8, cudaMemcpyHostToDevice));
+    h->po.zir = h->zir.as<double>();
+    h->po.n_zir = n;
+  }
   const int max_push = cfg->max_push_rows > 0 ? cfg->max_push_rows : 4096;
   h->cap_rows = std::max(cfg->frame_len, h->overlap + max_push);
   const int C = cfg->n_channels;
@@ -436,7 +534,7 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
 extern "C" int hga_destroy(hga_handle* h) {
   if (!h) return HGA_OK;
   cudaSetDevice(h->cfg.device);
-  for (DevBuf* b : {&h->state, &h->framebuf, &h->state2, &h->framebuf2, &h->work, &h->segs, &h->ybuf, &h->stats_part, &h->seg_state, &h->seg_rem,
+  for (DevBuf* b : {&h->state, &h->framebuf, &h->state2, &h->framebuf2, &h->work, &h->segs, &h->ybuf, &h->stats_part, &h->seg_state, &h->seg_rem, &h->zir,
                     &h->xdev, &h->outdev, &h->mudev, &h->sigdev})
     b->release();
   h->pin_in.release();
@@ -579,7 +677,7 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
     const int cg = (C + 31) / 32;
     int64_t slots = 0;
     if (variant == 0) slots = std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
-    else if (variant == 1) slots = pipe_item_slots(h->q, h->pc, h->cfg.precision, h->cfg.hop, h->n_sm, C);
+    else if (variant == 1) slots = pipe_item_slots(h->q, h->po, h->cfg.precision, h->cfg.hop, h->n_sm, C);
     plan_chunks(h, n_seg, seg_start, seg_len, out_row, slots, fused);
     if ((rc = upload_plan(h, st))) return rc;
     h->plan_key = key;
@@ -590,7 +688,7 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
     for (int i = 0; i < n_seg; ++i) { xlo = std::min(xlo, seg_start[i]); xhi = std::max(xhi, seg_start[i] + seg_len[i]); }
     FusedArgs a{x, ldx, h->work.as<Work>(), (int)h->work_host.size(), C, L, hop, h->nb, h->cfg.eps, mu, sigma, out, ldo, state_in, rem_in, state_out, rem_out, xlo, xhi, nullptr};
     if (h->timing) CU(cudaEventRecord(h->ev0, st));
-    if (variant == 1) rc = launch_pipe(h->q, h->pc, h->cfg.precision, a, st);
+    if (variant == 1) rc = launch_pipe(h->q, h->po, h->cfg.precision, a, st);
     else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, st);
     else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, st);
     else rc = launch_fused_seq<kFused>(h, a, st);
@@ -1062,7 +1160,7 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     if (variant == -3) return fail(HGA_ERR_UNSUPPORTED, "f32 precision needs the standard 8+8-section unit-gain cascade and hop 10 or 20");
     if (key != h->plan_key || variant != h->plan_variant) {
       const int cg = (C + 31) / 32;
-      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->pc, h->cfg.precision, h->cfg.hop, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
+      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->po, h->cfg.precision, h->cfg.hop, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
       plan_chunks(h, n_segments, seg_start, seg_len, out_row, slots, true);
       if ((rc = upload_plan(h, sk))) return rc;
       h->plan_key = key;
@@ -1092,7 +1190,7 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     CU(cudaEventRecord(e_up, sc));
     CU(cudaStreamWaitEvent(sk, e_up, 0));
     FusedArgs a{xd, C, h->work.as<Work>() + next, (int)(end - next), C, L, hop, h->nb, h->cfg.eps, mu_d, sig_d, od, C, nullptr, nullptr, nullptr, nullptr, lo, hi, nullptr};
-    if (variant == 1) rc = launch_pipe(h->q, h->pc, h->cfg.precision, a, sk);
+    if (variant == 1) rc = launch_pipe(h->q, h->po, h->cfg.precision, a, sk);
     else if (is_unit_std(h->q)) rc = launch_fused_seq<kUnitStd>(h, a, sk);
     else if (h->q.unit) rc = launch_fused_seq<kUnit>(h, a, sk);
     else rc = launch_fused_seq<kFused>(h, a, sk);

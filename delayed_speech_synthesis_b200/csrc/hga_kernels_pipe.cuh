@@ -27,6 +27,11 @@ struct PipeConst {  // compile-time-indexable, warp-uniform operands (constant b
   double zu0[kMaxSec], zu1[kMaxSec];  // sosfilt_zi divided by the gains in front of each section
   double pow_scale;                   // G^2 / L
   unsigned long long na1p[kMaxSec], na2p[kMaxSec], b1p[kMaxSec];  // (-a1,-a1), (-a2,-a2), (b1u,b1u) as float32 pairs
+  // k_hga_pipe2 only (build_pipe2_const): the same three operands as doubles, in the kernel's own section order and with
+  // the signs its section forms use (hga_kernels_pipe2.cuh, "section forms"); na1p / na2p / b1p then hold their float32 pairs.
+  double c1d[kMaxSec], c2d[kMaxSec], cbd[kMaxSec];
+  unsigned amask;  // bit s set: section s has numerator [1, 0, -1] (3-slot form)
+  int pad_;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -73,6 +78,11 @@ __device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) { asm("mo
 __device__ __forceinline__ f32x2 operator+(f32x2 a, f32x2 b) {
   f32x2 r;
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f32x2 operator-(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
   return r;
 }
 using ::fma;  // keep the scalar overloads visible next to the packed one

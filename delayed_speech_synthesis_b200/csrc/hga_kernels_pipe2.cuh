@@ -61,12 +61,15 @@ __device__ __forceinline__ double tab_log(double x, const double* __restrict__ t
 template <int S, int TB, typename T>
 struct Pipe2Smem {
   static constexpr int CPL = PipeTraits<T>::CPL;
-  static constexpr int NX = 3;    // TMA ring depth
-  static constexpr int NB = 2;    // buffers per internal link
+  static constexpr int NX = PipeTraits<T>::CPL == 1 ? 4 : 3;  // TMA ring depth (float32 mode: 20 KB tiles, no room for a 4th)
+#ifndef HGA_PIPE2_NB64
+#define HGA_PIPE2_NB64 3
+#endif
+  static constexpr int NB = PipeTraits<T>::CPL == 1 ? HGA_PIPE2_NB64 : 2;  // buffers per internal link
   static constexpr int NBY = 4;   // y tiles (filter warp S-1 -> framing warps)
   static constexpr int kBsRing = TB / 10 >= 4 ? 32 : 16;  // hop-block sums kept (framing warps may be two tiles apart)
   static constexpr int NBS = 4;   // block-sum hand-off barriers (phase A of tile m -> phase B of tile m)
-  static constexpr int NBC = 3;   // float32 mode: converted x tiles (framing warps -> filter warp 0)
+  static constexpr int NBC = NX;  // float32 mode: converted x tiles (framing warps -> filter warp 0)
   static constexpr size_t x_bytes = (size_t)NX * TB * 32 * CPL * 8;
   static constexpr size_t c_bytes = CPL == 2 ? (size_t)NBC * TB * 32 * sizeof(T) : 0;
   static constexpr int NL = S - 1;  // links between filter warps
@@ -82,82 +85,82 @@ struct Pipe2Smem {
   static constexpr size_t total = bar_off + (size_t)n_bars * 8;
 };
 
-// Section coefficients of one filter warp, held in registers so that every filter warp of a CTA executes the SAME
-// instructions: two warps of an SM sub-partition running different copies of the loop thrash its instruction buffer
-// (tools/microbench/cascade_rates: 38.6 -> 56.6 cycles per row for two float64 warps with per-warp code).
-template <typename T, int NS>
-struct SecCoef {
-  T na1[NS], na2[NS], b1[NS];
+// Section forms.  Every section runs on the gain-free signal (see hga_kernels_pipe.cuh); its three operands c1, c2, cb
+// come from PipeConst (c1d / c2d / cbd as doubles, na1p / na2p / b1p as float32 pairs), filled by build_pipe2_const:
+//   U  numerator [1, b1, 1], transposed direct form II:   y = x + z0;  z0' = (-a1) y + (b1 x + z1);  z1' = (-a2) y + x
+//        operands c1 = -a1, c2 = -a2, cb = b1: 1 ADD + 3 FMA
+//   A  numerator [1, 0, -1] (a zero at DC and one at Nyquist), same form on the NEGATED state v = -z0, w = -z1:
+//        y = x - v;  v' = a1 y + w;  w' = a2 y + x        operands c1 = +a1, c2 = +a2: 1 ADD + 2 FMA
+// The reference's band-pass has numerator (1 + z^-1)^8 (1 - z^-1)^8 = (1 - z^-2)^8 (four sections [1, 2, 1], four
+// [1, -2, 1]); paired as eight A sections it is the same transfer function with 8 FP slots fewer
+// per channel-sample (56 instead of 64).  Re-pairing changes what the section states mean, so the kernel never loads the
+// reference's initial state: every item starts from ZERO state and, for items that begin a segment, the zero-input
+// response of sosfilt_zi (one sequence for all channels, FusedArgs::zir) is added to the filtered rows (linearity).
+// AM = bit mask of the A sections among the NS sections of a filter warp (the same for every warp, so that all filter
+// warps do the same amount of work: the host interleaves the sections [A, A, U, U] per warp).
+template <typename T> struct P2Op;
+template <> struct P2Op<double> {
+  static __device__ __forceinline__ double c1(const PipeConst& p, int s) { return p.c1d[s]; }
+  static __device__ __forceinline__ double c2(const PipeConst& p, int s) { return p.c2d[s]; }
+  static __device__ __forceinline__ double cb(const PipeConst& p, int s) { return p.cbd[s]; }
 };
-template <int NS>
-__device__ __forceinline__ void load_coef_any(const Cascade& q, const PipeConst&, int g, SecCoef<double, NS>& c) {
-#pragma unroll
-  for (int s = 0; s < NS; ++s) {
-    c.na1[s] = -q.a1[g * NS + s];
-    c.na2[s] = -q.a2[g * NS + s];
-    c.b1[s] = q.b1u[g * NS + s];
-  }
-}
-template <int NS>
-__device__ __forceinline__ void load_coef_any(const Cascade&, const PipeConst& pc, int g, SecCoef<f32x2, NS>& c) {
-#pragma unroll
-  for (int s = 0; s < NS; ++s) {
-    c.na1[s] = f32x2{pc.na1p[g * NS + s]};
-    c.na2[s] = f32x2{pc.na2p[g * NS + s]};
-    c.b1[s] = f32x2{pc.b1p[g * NS + s]};
-  }
-}
+template <> struct P2Op<f32x2> {
+  static __device__ __forceinline__ f32x2 c1(const PipeConst& p, int s) { return f32x2{p.na1p[s]}; }
+  static __device__ __forceinline__ f32x2 c2(const PipeConst& p, int s) { return f32x2{p.na2p[s]}; }
+  static __device__ __forceinline__ f32x2 cb(const PipeConst& p, int s) { return f32x2{p.b1p[s]}; }
+};
 // Coefficient source of a filter warp.  G >= 0: the section group is a compile-time constant, coefficients are
 // constant-bank / uniform-register operands (fastest arithmetic: FFMA2 with three register operands runs ~20 % slower),
 // but every group is its own copy of the code, so it is only used when each SM sub-partition runs ONE group (S == 4:
-// warp g sits on sub-partition g).  G == -1: run-time group, coefficients in registers, one copy of the code.
+// warp g sits on sub-partition g; two warps of a sub-partition running different copies of the loop thrash its
+// instruction buffer, tools/microbench/cascade_rates).  G == -1: run-time group, coefficients in registers, one copy.
 template <typename T, int NS, int G>
 struct Coef {
-  const Cascade& q;
   const PipeConst& pc;
-  __device__ __forceinline__ Coef(const Cascade& q_, const PipeConst& pc_, int) : q(q_), pc(pc_) {}
-  __device__ __forceinline__ T na1(int s) const { return PipeTraits<T>::na1(q, pc, G * NS + s); }
-  __device__ __forceinline__ T na2(int s) const { return PipeTraits<T>::na2(q, pc, G * NS + s); }
-  __device__ __forceinline__ T b1(int s) const { return PipeTraits<T>::b1(q, pc, G * NS + s); }
+  __device__ __forceinline__ Coef(const Cascade&, const PipeConst& pc_, int) : pc(pc_) {}
+  __device__ __forceinline__ T na1(int s) const { return P2Op<T>::c1(pc, G * NS + s); }
+  __device__ __forceinline__ T na2(int s) const { return P2Op<T>::c2(pc, G * NS + s); }
+  __device__ __forceinline__ T b1(int s) const { return P2Op<T>::cb(pc, G * NS + s); }
 };
 template <typename T, int NS>
 struct Coef<T, NS, -1> {
-  SecCoef<T, NS> c;
-  __device__ __forceinline__ Coef(const Cascade& q, const PipeConst& pc, int g) { load_coef_any<NS>(q, pc, g, c); }
-  __device__ __forceinline__ T na1(int s) const { return c.na1[s]; }
-  __device__ __forceinline__ T na2(int s) const { return c.na2[s]; }
-  __device__ __forceinline__ T b1(int s) const { return c.b1[s]; }
+  T c1[NS], c2[NS], cb[NS];
+  __device__ __forceinline__ Coef(const Cascade&, const PipeConst& pc, int g) {
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      c1[s] = P2Op<T>::c1(pc, g * NS + s);
+      c2[s] = P2Op<T>::c2(pc, g * NS + s);
+      cb[s] = P2Op<T>::cb(pc, g * NS + s);
+    }
+  }
+  __device__ __forceinline__ T na1(int s) const { return c1[s]; }
+  __device__ __forceinline__ T na2(int s) const { return c2[s]; }
+  __device__ __forceinline__ T b1(int s) const { return cb[s]; }
 };
 
-// One wavefront step (see wave_step in hga_kernels_pipe.cuh) with register coefficients; sections s <= jmax active
-// (jmax >= NS - 1: all of them; smaller only during the first NS - 1 steps of a fresh stream).
-template <typename T, int NS, bool MASKED, typename CF>
-__device__ __forceinline__ T wave_step_r(const CF& c, T x0, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS], int jmax) {
-  T xin[NS], yn[NS], t[NS], n0[NS], n1[NS];
+// One wavefront step (see wave_step in hga_kernels_pipe.cuh): section s consumes the output its predecessor produced in
+// the PREVIOUS step, so the NS section updates of a step are mutually independent.
+template <typename T, int NS, unsigned AM, typename CF>
+__device__ __forceinline__ T wave_step_r(const CF& c, T x0, T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
+  T xin[NS], yn[NS], t[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) xin[s] = s == 0 ? x0 : yp[s - 1];
 #pragma unroll
-  for (int s = 0; s < NS; ++s) yn[s] = xin[s] + z0[s];
+  for (int s = 0; s < NS; ++s) yn[s] = ((AM >> s) & 1u) ? xin[s] - z0[s] : xin[s] + z0[s];
 #pragma unroll
-  for (int s = 0; s < NS; ++s) t[s] = fma(c.b1(s), xin[s], z1[s]);
+  for (int s = 0; s < NS; ++s) t[s] = ((AM >> s) & 1u) ? z1[s] : fma(c.b1(s), xin[s], z1[s]);
 #pragma unroll
-  for (int s = 0; s < NS; ++s) n0[s] = fma(c.na1(s), yn[s], t[s]);
+  for (int s = 0; s < NS; ++s) z0[s] = fma(c.na1(s), yn[s], t[s]);
 #pragma unroll
-  for (int s = 0; s < NS; ++s) n1[s] = fma(c.na2(s), yn[s], xin[s]);
+  for (int s = 0; s < NS; ++s) z1[s] = fma(c.na2(s), yn[s], xin[s]);
 #pragma unroll
-  for (int s = 0; s < NS; ++s) {
-    if (!MASKED || jmax >= s) {
-      z0[s] = n0[s];
-      z1[s] = n1[s];
-      yp[s] = yn[s];
-    }
-  }
+  for (int s = 0; s < NS; ++s) yp[s] = yn[s];
   return yp[NS - 1];
 }
 
 // One full tile through the sections of a warp: in-tile row i -> out-tile row i (the out tile is the stream shifted by
 // NS-1 more rows than the in tile).  Loop body = 2U rows, next U input rows loaded while the current U are filtered.
-template <typename T, int NS, int TB, typename CF>
+template <typename T, int NS, int TB, unsigned AM = 0u, typename CF>
 __device__ __forceinline__ void pipe2_tile(const CF& c, const T* __restrict__ in, T* __restrict__ out,
                                            T (&yp)[NS], T (&z0)[NS], T (&z1)[NS]) {
   constexpr int U = (TB % 10 == 0) ? 5 : 4;
@@ -170,19 +173,19 @@ __device__ __forceinline__ void pipe2_tile(const CF& c, const T* __restrict__ in
 #pragma unroll
     for (int u = 0; u < U; ++u) vb[u] = in[(k + U + u) * 32];
 #pragma unroll
-    for (int u = 0; u < U; ++u) out[(k + u) * 32] = wave_step_r<T, NS, false>(c, va[u], yp, z0, z1, NS);
+    for (int u = 0; u < U; ++u) out[(k + u) * 32] = wave_step_r<T, NS, AM>(c, va[u], yp, z0, z1);
     if (k + 2 * U < TB) {
 #pragma unroll
       for (int u = 0; u < U; ++u) va[u] = in[(k + 2 * U + u) * 32];
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) out[(k + U + u) * 32] = wave_step_r<T, NS, false>(c, vb[u], yp, z0, z1, NS);
+    for (int u = 0; u < U; ++u) out[(k + U + u) * 32] = wave_step_r<T, NS, AM>(c, vb[u], yp, z0, z1);
   }
 }
 
 // Filter warp g of a CTA (g is a run-time value: one copy of this code serves all filter warps): sections
 // [g*NS, (g+1)*NS) over every tile of the work item.
-template <typename T, int S, int TB, int E, int G>
+template <typename T, int S, int TB, int E, int G, unsigned AM>
 __device__ __forceinline__ void pipe2_filter_warp(const Cascade& q, const PipeConst& pc, const CUtensorMap* tmap, unsigned char* base, int ntiles,
                                                   bool fresh, int g_rt, int c0, int row_first, int lane, long long* pr, bool prof) {
   const int g = G >= 0 ? G : g_rt;
@@ -196,9 +199,7 @@ __device__ __forceinline__ void pipe2_filter_warp(const Cascade& q, const PipeCo
   T* links = (T*)(base + SM::link_off);
   T* ylink = (T*)(base + SM::y_off);
   uint64_t* bars = (uint64_t*)(base + SM::bar_off);
-  uint64_t* full_x = bars + SM::b_full_x;
   const bool first = g == 0, last = g == S - 1;
-  const int d_in = E + g * (NS - 1);
 
   // ring bases, barriers and depths of this warp's input and output
   const T* in_base = (first ? (CONV ? cring : xring) : links + (size_t)(g - 1) * NB * TB * 32) + lane;
@@ -208,14 +209,13 @@ __device__ __forceinline__ void pipe2_filter_warp(const Cascade& q, const PipeCo
   uint64_t* out_full0 = bars + (last ? SM::b_full_y : SM::b_full_l + g * NB);
   uint64_t* out_empty0 = bars + (last ? SM::b_empty_y : SM::b_empty_l + g * NB);
   const int nin = first ? (CONV ? NBC : NX) : NB, nout = last ? NBY : NB;
-  const bool xin = first && !CONV;  // this warp consumes the TMA ring itself and refills it
 
   const Coef<T, NS, G> c(q, pc, g);
   T z0[NS], z1[NS], yp[NS];
 #pragma unroll
   for (int s = 0; s < NS; ++s) {
-    z0[s] = fresh ? TR::splat(pc.zu0[g * NS + s]) : TR::zero();
-    z1[s] = fresh ? TR::splat(pc.zu1[g * NS + s]) : TR::zero();
+    z0[s] = TR::zero();  // every item starts from zero state (fresh items: + FusedArgs::zir in the framing warps)
+    z1[s] = TR::zero();
     yp[s] = TR::zero();
   }
   long long tk = prof ? clock64() : 0;
@@ -234,21 +234,18 @@ __device__ __forceinline__ void pipe2_filter_warp(const Cascade& q, const PipeCo
     HGA_TICK2(4)
     const T* in = in_base + (size_t)si * TB * 32;
     T* out = out_base + (size_t)so * TB * 32;
-    if (m == 0 && fresh) {
-      for (int i = d_in; i < TB; ++i) out[i * 32] = wave_step_r<T, NS, true>(c, in[i * 32], yp, z0, z1, i - d_in);
-    } else {
-      pipe2_tile<T, NS, TB>(c, in, out, yp, z0, z1);
+    if (m == 0 && fresh && first) {
+      // the E rows in front of a segment are not part of it (they may hold the previous segment): the stream starts at 0
+      T* inw = const_cast<T*>(in);
+#pragma unroll
+      for (int i = 0; i < E; ++i) inw[i * 32] = TR::zero();  // both modes: this warp's input rows hold 32 T
+      __syncwarp();
     }
+    pipe2_tile<T, NS, TB, AM>(c, in, out, yp, z0, z1);
     __syncwarp();
     if (lane == 0) {
       mbar_arrive(out_full0 + so);
-      if (!xin) {
-        mbar_arrive(in_empty0 + si);
-      } else if (m + NX < ntiles) {  // filter warp 0 refills the slot it has just consumed
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&full_x[si], (uint32_t)(TB * 32 * CPL * 8));
-        tma_load_2d(xring + (size_t)si * TB * 32, tmap, c0, row_first + (m + NX) * TB, &full_x[si]);
-      }
+      mbar_arrive(in_empty0 + si);  // float64 mode, warp 0: releases the TMA slot to the producer warp
     }
     if (++si == nin) { si = 0; pi ^= 1; }
     if (++so == nout) { so = 0; po ^= 1; }
@@ -313,8 +310,8 @@ __device__ __forceinline__ void pipe2_convert_tile(const CUtensorMap* tmap, unsi
 }
 
 // One CTA = one (work item, group of 32 * CPL channels): warps [0, S) filter, warps [S, S + NF) frame.
-template <typename T, int S, int TB, int HOP, int NF, bool PERG>
-__global__ void __launch_bounds__(32 * (S + NF), 1) k_hga_pipe2(const __grid_constant__ Cascade q, const __grid_constant__ PipeConst pc,
+template <typename T, int S, int TB, int HOP, int NF, bool PERG, unsigned AM>
+__global__ void __launch_bounds__(32 * (S + NF + 1), 1) k_hga_pipe2(const __grid_constant__ Cascade q, const __grid_constant__ PipeConst pc,
                                                                  const __grid_constant__ FusedArgs a, const __grid_constant__ CUtensorMap tmap) {
   constexpr int NS = kMaxSec / S;
   using SM = Pipe2Smem<S, TB, T>;
@@ -367,12 +364,25 @@ __global__ void __launch_bounds__(32 * (S + NF), 1) k_hga_pipe2(const __grid_con
   if (g < S) {
     if (PERG) {
 #define HGA_FW(G_) \
-  if (g == G_) pipe2_filter_warp<T, S, TB, E, (G_ < S ? G_ : 0)>(q, pc, &tmap, base, ntiles, fresh, g, c0, row_first, lane, pr, prof);
+  if (g == G_) pipe2_filter_warp<T, S, TB, E, (G_ < S ? G_ : 0), AM>(q, pc, &tmap, base, ntiles, fresh, g, c0, row_first, lane, pr, prof);
       HGA_FW(0) HGA_FW(1) HGA_FW(2) HGA_FW(3)
       if (S > 4) { HGA_FW(4) HGA_FW(5) HGA_FW(6) HGA_FW(7) }
 #undef HGA_FW
     } else {
-      pipe2_filter_warp<T, S, TB, E, -1>(q, pc, &tmap, base, ntiles, fresh, g, c0, row_first, lane, pr, prof);
+      pipe2_filter_warp<T, S, TB, E, -1, AM>(q, pc, &tmap, base, ntiles, fresh, g, c0, row_first, lane, pr, prof);
+    }
+  } else if (g == S + NF) {
+    // ------------------------------------------------------------------ TMA producer warp (float64 mode; in float32 mode
+    // the converting framing warps are the consumers of the x ring and refill it themselves)
+    if (CPL == 1 && lane == 0) {
+      uint64_t* empty_x = bars + SM::b_empty_x;
+      for (int m = NX; m < ntiles; ++m) {
+        const int sx = m % NX;
+        mbar_wait(&empty_x[sx], ((m / NX) - 1) & 1);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&full_x[sx], kTileBytes);
+        tma_load_2d(xring + (size_t)sx * TB * CW, &tmap, c0, row_first + m * TB, &full_x[sx]);
+      }
     }
   } else {
     // ------------------------------------------------------------------ framing warps
@@ -422,10 +432,15 @@ __global__ void __launch_bounds__(32 * (S + NF), 1) k_hga_pipe2(const __grid_con
           const int64_t brel = brel0 + j, tb = wk.t_begin + brel * HOP;
           if (brel >= 0 && tb >= wk.t_acc && tb + HOP <= wk.t_end) {
             double bsum;
+            const bool add_zir = fresh && tb < a.n_zir;  // n_zir is a multiple of HOP: the whole block is inside
             if (CPL == 1) {
               double v[HOP];
 #pragma unroll
               for (int i = 0; i < HOP; ++i) v[i] = TR::load_part(yt + (j * HOP + i) * 32, p);
+              if (add_zir) {
+#pragma unroll
+                for (int i = 0; i < HOP; ++i) v[i] += a.zir[tb + i];
+              }
               double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
               for (int i = 0; i < HOP; i += 2) {
@@ -440,6 +455,10 @@ __global__ void __launch_bounds__(32 * (S + NF), 1) k_hga_pipe2(const __grid_con
               float v[HOP];
 #pragma unroll
               for (int i = 0; i < HOP; ++i) v[i] = yf[i * 64];
+              if (add_zir) {
+#pragma unroll
+                for (int i = 0; i < HOP; ++i) v[i] += (float)a.zir[tb + i];
+              }
               float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
               for (int i = 0; i < HOP; i += 2) {
