@@ -202,6 +202,10 @@ def test_offline_2khz_high_density_prefix(torch):
     got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
     assert got.shape == ref.shape == (2996, C)
     assert _err(got, ref)[0] <= TOL_F64
+    # float32 cascade at 2 kHz: the notch poles sit at radius 0.9988 (0.9976 at 1 kHz), rounding noise is amplified more;
+    # stated tolerance at this rate 5e-4 max-abs per feature (observed 2.6e-4 on white noise)
+    got32 = HgaEngine(fs, C, precision="f32").extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert _err(got32, ref)[0] <= 5 * TOL_F32
 
 
 def test_offline_rejects_short_segment():
