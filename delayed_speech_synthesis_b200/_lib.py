@@ -61,6 +61,9 @@ SIGNATURES = {
     "hga_chanmap_destroy": (C.c_int, [_vp]),
     "hga_chanmap_apply": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64, _vp]),
     "hga_chanmap_apply_host": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64]),
+    "hga_packet_header": (C.c_int, [_vp, _i64, _pi32, _pi32]),
+    "hga_packet_decode": (C.c_int, [_i32, _vp, _i64, _vp, _i64, _vp]),
+    "hga_stream_push_packet": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _vp, C.POINTER(_i64)]),
     "hga_launch_count": (_i64, []),
     "hga_set_timing": (C.c_int, [_vp, _i32]),
     "hga_last_kernel_ms": (_dbl, [_vp]),

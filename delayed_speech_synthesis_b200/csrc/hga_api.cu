@@ -92,7 +92,7 @@ struct PinBuf {
     if (p) cudaFreeHost(p);
     p = nullptr;
     cap = 0;
-    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocMapped | cudaHostAllocPortable);  // mapped: the zero-copy packet path reads / writes it from the kernel
     if (e != cudaSuccess) {
       cudaGetLastError();
       return fail(HGA_ERR_NOMEM, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
@@ -107,7 +107,21 @@ struct PinBuf {
   }
   template <class T>
   T* as() const { return static_cast<T*>(p); }
+  template <class T>
+  T* dev() const {  // the same buffer as the current device sees it
+    void* d = nullptr;
+    if (!p || cudaHostGetDevicePointer(&d, p, 0) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return static_cast<T*>(d);
+  }
 };
+// Packets of at most this many rows go through the zero-copy path: the kernel reads the packet from mapped pinned host
+// memory (staged into shared memory) and writes the frames to mapped pinned host memory: one launch + one stream
+// synchronisation per packet instead of H2D copy + launch + D2H copy + synchronisation.  HGA_B200_STREAM_MAPPED=0 disables.
+constexpr int64_t kMappedRows = 64;
+static bool stream_mapped() {
+  static const bool on = [] { const char* e = getenv("HGA_B200_STREAM_MAPPED"); return !(e && atoi(e) == 0); }();
+  return on;
+}
 
 // ------------------------------------------------------------------------------------------------ cascade set-up
 // Fill a Cascade from one or two scipy SOS matrices (rows [b0 b1 b2 a0 a1 a2], a0 == 1).
@@ -787,6 +801,31 @@ static int bulk_push(hga_handle* h, const double* x, int64_t n, int64_t ldx, con
   return HGA_OK;
 }
 
+// One packet through the latency kernels.  xf != nullptr: float32 [C][n] payload in place of x.  Small packets take
+// k_stream_push_sys (sections across lanes, frame rows and packet in shared memory), the rest k_stream_push.
+static void launch_stream(hga_handle* h, const PushGeom& g, const double* x, const float* xf, int64_t ldx, int64_t n, const double* mu,
+                          const double* sigma, double* out, int64_t ldo, float* out_f32, cudaStream_t st) {
+  const int C = h->cfg.n_channels;
+  static const bool fast_on = [] { const char* e = getenv("HGA_B200_STREAM_FAST"); return !(e && atoi(e) == 0); }();
+  if (fast_on && g.rows_total + n <= kStreamFastRows) {
+    const size_t smem = (size_t)kSysWarps * (g.rows_total + n) * 2 * 8;  // <= 12 KB
+    const unsigned grid = (unsigned)((C + 2 * kSysWarps - 1) / (2 * kSysWarps));
+    if (xf)
+      k_stream_push_sys<1><<<grid, 32 * kSysWarps, smem, st>>>(h->q, xf, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
+                                                                g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
+                                                                h->cfg.eps, mu, sigma, out, ldo, out_f32);
+    else
+      k_stream_push_sys<0><<<grid, 32 * kSysWarps, smem, st>>>(h->q, x, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
+                                                                g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
+                                                                h->cfg.eps, mu, sigma, out, ldo, out_f32);
+  } else {
+    k_stream_push<<<(C + 31) / 32, 32, 0, st>>>(h->q, x, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
+                                                g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
+                                                h->cfg.eps, mu, sigma, out, ldo, xf, out_f32);
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  h->first_frame = 0;
+}
 static int stream_push_dev(hga_handle* h, const double* x, int64_t n, int64_t ldx, const double* mu, const double* sigma,
                            double* out, int64_t ldo, int64_t* n_frames, cudaStream_t st) {
   const int C = h->cfg.n_channels;
@@ -795,11 +834,8 @@ static int stream_push_dev(hga_handle* h, const double* x, int64_t n, int64_t ld
   if ((mu == nullptr) != (sigma == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
   const PushGeom g = push_geom(h, n);
   if (n > kBulkRows && !(h->first_frame && n < h->cfg.frame_len)) return bulk_push(h, x, n, ldx, mu, sigma, out, ldo, n_frames, st, g);
-  k_stream_push<<<(C + 31) / 32, 32, 0, st>>>(h->q, x, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
-                                              g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
-                                              h->cfg.eps, mu, sigma, out, ldo);
-  LAUNCHED();
-  h->first_frame = 0;
+  launch_stream(h, g, x, nullptr, ldx, n, mu, sigma, out, ldo, nullptr, st);
+  CU(cudaGetLastError());
   if (n_frames) *n_frames = g.frames;
   return HGA_OK;
 }
@@ -867,10 +903,103 @@ extern "C" int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t
   double* pin = h->pin_in.as<double>();
   if (ldx == C) memcpy(pin, x_host, in_bytes);
   else for (int64_t r = 0; r < n; ++r) memcpy(pin + r * C, x_host + r * ldx, (size_t)C * 8);
-  CU(cudaMemcpyAsync(h->xdev.p, pin, in_bytes, cudaMemcpyHostToDevice, st));
   int64_t nf = 0;
-  if ((rc = stream_push_dev(h, h->xdev.as<double>(), n, C, mu_d, sig_d, h->outdev.as<double>(), C, &nf, st))) return rc;
-  if (nf > 0) CU(cudaMemcpyAsync(h->pin_out.p, h->outdev.p, (size_t)nf * C * 8, cudaMemcpyDeviceToHost, st));
+  double* in_map = h->pin_in.dev<double>();
+  double* out_map = h->pin_out.dev<double>();
+  if (stream_mapped() && n <= kMappedRows && in_map && out_map) {  // zero-copy: see kMappedRows
+    launch_stream(h, g, in_map, nullptr, C, n, mu_d, sig_d, out_map, C, nullptr, st);
+    CU(cudaGetLastError());
+    nf = g.frames;
+  } else {
+    CU(cudaMemcpyAsync(h->xdev.p, pin, in_bytes, cudaMemcpyHostToDevice, st));
+    if ((rc = stream_push_dev(h, h->xdev.as<double>(), n, C, mu_d, sig_d, h->outdev.as<double>(), C, &nf, st))) return rc;
+    if (nf > 0) CU(cudaMemcpyAsync(h->pin_out.p, h->outdev.p, (size_t)nf * C * 8, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(st));
+  const double* po = h->pin_out.as<double>();
+  if (ldo == C) memcpy(out_host, po, (size_t)nf * C * 8);
+  else for (int64_t r = 0; r < nf; ++r) memcpy(out_host + r * ldo, po + r * C, (size_t)C * 8);
+  if (n_frames) *n_frames = nf;
+  return HGA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ wire packets
+// BCI2000 GenericSignal packet as the reference's ZMQ connector receives it (local/units.py:48,78-82; packed by
+// development_amplifier.py:14-25): struct '=BBB HH' (descriptor, supplement, dtype, n_channels, n_samples; 7 bytes,
+// native byte order, no padding) followed by n_channels * n_samples float32, channel-major.
+static int parse_packet(const void* packet, int64_t nbytes, int32_t* n_ch, int32_t* n_samp, const unsigned char** payload) {
+  if (!packet) return fail(HGA_ERR_INVALID, "null packet");
+  if (nbytes < 7) return fail(HGA_ERR_INVALID, "packet of %lld bytes is shorter than its 7-byte header", (long long)nbytes);
+  const unsigned char* b = static_cast<const unsigned char*>(packet);
+  uint16_t c, n;
+  memcpy(&c, b + 3, 2);
+  memcpy(&n, b + 5, 2);
+  if ((int64_t)c * n * 4 != nbytes - 7)
+    return fail(HGA_ERR_INVALID, "packet payload is %lld bytes, header says %u channels x %u samples float32", (long long)(nbytes - 7), c, n);
+  if (n_ch) *n_ch = c;
+  if (n_samp) *n_samp = n;
+  if (payload) *payload = b + 7;
+  return HGA_OK;
+}
+extern "C" int hga_packet_header(const void* packet_host, int64_t nbytes, int32_t* n_channels, int32_t* n_samples) {
+  return parse_packet(packet_host, nbytes, n_channels, n_samples, nullptr);
+}
+extern "C" int hga_packet_decode(int32_t device, const void* packet_host, int64_t nbytes, double* x_dev, int64_t ldx, void* stream) {
+  int32_t C = 0, n = 0;
+  const unsigned char* payload = nullptr;
+  int rc = parse_packet(packet_host, nbytes, &C, &n, &payload);
+  if (rc) return rc;
+  if (!x_dev || ldx < C) return fail(HGA_ERR_INVALID, "bad output: ldx=%lld for %d channels", (long long)ldx, C);
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  if (C == 0 || n == 0) return HGA_OK;
+  CU(cudaSetDevice(device));
+  cudaStream_t st = (cudaStream_t)stream;
+  float* tmp = nullptr;
+  const size_t bytes = (size_t)C * n * 4;
+  CU(cudaMallocAsync((void**)&tmp, bytes, st));
+  CU(cudaMemcpyAsync(tmp, payload, bytes, cudaMemcpyHostToDevice, st));  // pageable, unaligned source: staged by the driver
+  k_packet_rows<<<dim3((C + 31) / 32, (n + 31) / 32), 256, 0, st>>>(tmp, C, n, x_dev, ldx);
+  LAUNCHED();
+  CU(cudaFreeAsync(tmp, st));
+  return HGA_OK;
+}
+// One packet through a long-lived extractor: payload -> pinned staging -> H2D -> ONE kernel that reads the float32
+// channel-major payload directly (no transposed float64 copy is ever made) -> D2H of the frames.
+extern "C" int hga_stream_push_packet(hga_handle* h, const void* packet_host, int64_t nbytes, const double* mu_host, const double* sigma_host,
+                                      double* out_host, int64_t ldo, float* out_f32_dev, int64_t* n_frames) {
+  if (!h || !out_host) return fail(HGA_ERR_INVALID, "null argument");
+  int32_t Cp = 0, np_ = 0;
+  const unsigned char* payload = nullptr;
+  int rc = parse_packet(packet_host, nbytes, &Cp, &np_, &payload);
+  if (rc) return rc;
+  const int C = h->cfg.n_channels;
+  const int64_t n = np_;
+  if (Cp != C) return fail(HGA_ERR_INVALID, "packet has %d channels, extractor has %d", Cp, C);
+  if (ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  if (n < 1 || n > kBulkRows || n + h->overlap > h->cap_rows) return fail(HGA_ERR_INVALID, "packet of %lld samples outside [1, min(max_push_rows, %lld)]", (long long)n, (long long)kBulkRows);
+  CU(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = h->s_own;
+  const PushGeom g = push_geom(h, n);
+  const size_t in_bytes = (size_t)n * C * 4, out_bytes = (size_t)std::max<int64_t>(1, g.frames) * C * 8;
+  if ((rc = h->pin_in.reserve(in_bytes)) || (rc = h->pin_out.reserve(out_bytes)) || (rc = h->xdev.reserve(in_bytes)) ||
+      (rc = h->outdev.reserve(out_bytes)))
+    return rc;
+  const double *mu_d, *sig_d;
+  if ((rc = sync_musigma(h, mu_host, sigma_host, st, &mu_d, &sig_d))) return rc;
+  memcpy(h->pin_in.p, payload, in_bytes);
+  const int64_t nf = g.frames;
+  float* in_map = h->pin_in.dev<float>();
+  double* out_map = h->pin_out.dev<double>();
+  if (stream_mapped() && n <= kMappedRows && in_map && out_map) {
+    launch_stream(h, g, nullptr, in_map, C, n, mu_d, sig_d, out_map, C, out_f32_dev, st);
+    CU(cudaGetLastError());
+  } else {
+    CU(cudaMemcpyAsync(h->xdev.p, h->pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
+    launch_stream(h, g, nullptr, h->xdev.as<float>(), C, n, mu_d, sig_d, h->outdev.as<double>(), C, out_f32_dev, st);
+    CU(cudaGetLastError());
+    if (nf > 0) CU(cudaMemcpyAsync(h->pin_out.p, h->outdev.p, (size_t)nf * C * 8, cudaMemcpyDeviceToHost, st));
+  }
+  h->first_frame = 0;
   CU(cudaStreamSynchronize(st));
   const double* po = h->pin_out.as<double>();
   if (ldo == C) memcpy(out_host, po, (size_t)nf * C * 8);

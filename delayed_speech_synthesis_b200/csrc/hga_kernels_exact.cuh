@@ -115,8 +115,28 @@ __global__ void __launch_bounds__(32) k_stream_push(const __grid_constant__ Casc
                                                     int rows_total, int overlap, int n_frames, int L, int hop,
                                                     double eps, const double* __restrict__ mu,
                                                     const double* __restrict__ sigma, double* __restrict__ out,
-                                                    int64_t ldo) {
+                                                    int64_t ldo, const float* __restrict__ xf = nullptr,
+                                                    float* __restrict__ out_f32 = nullptr, int staged = 0) {
+  // xf != nullptr: the input is the payload of a wire packet, float32 [C][n] channel-major (local/units.py:78-82:
+  // frombuffer(float32).reshape(n_channels, n_samples), transposed, upcast to float64) read in place of x.
+  // out_f32 != nullptr: the frames are also written as float32 (n_frames, C) for the nVAD's `.float()` (local/units.py:433).
+  // staged != 0: x / xf is host memory mapped into the device's address space (zero-copy packet path): the block's 32
+  // channels x n samples are first pulled into shared memory with coalesced reads, all of them in flight at once, so the
+  // packet crosses PCIe in one round trip instead of one dependent read per sample.  Dynamic shared memory: n * 32 * 8 B.
+  extern __shared__ __align__(16) unsigned char stage_raw[];
   const int c = blockIdx.x * 32 + threadIdx.x;
+  if (staged) {
+    if (xf != nullptr) {
+      float* sf = reinterpret_cast<float*>(stage_raw);
+      const int c0 = blockIdx.x * 32, cnt = min(32, C - c0) * n;
+      const float* src = xf + (int64_t)c0 * n;
+      for (int i = threadIdx.x; i < cnt; i += 32) sf[i] = src[i];
+    } else if (c < C) {
+      double* sd = reinterpret_cast<double*>(stage_raw);
+      for (int t = 0; t < n; ++t) sd[t * 32 + threadIdx.x] = x[(int64_t)t * ldx + c];
+    }
+    __syncwarp();
+  }
   if (c >= C) return;
   double z0[kMaxSec], z1[kMaxSec];
 #pragma unroll
@@ -127,8 +147,19 @@ __global__ void __launch_bounds__(32) k_stream_push(const __grid_constant__ Casc
   double* bp = buf + c;
   for (int r = 0; r < zero_rows; ++r) bp[(int64_t)r * C] = 0.0;
   const double* xp = x + c;
-  for (int t = 0; t < n; ++t)
-    bp[(int64_t)(y_row0 + t) * C] = cascade<kExact, 0, kMaxSec>(q, xp[(int64_t)t * ldx], z0, z1);
+  if (staged && xf != nullptr) {
+    const float* fp = reinterpret_cast<const float*>(stage_raw) + threadIdx.x * n;
+    for (int t = 0; t < n; ++t) bp[(int64_t)(y_row0 + t) * C] = cascade<kExact, 0, kMaxSec>(q, (double)fp[t], z0, z1);
+  } else if (staged) {
+    const double* sp = reinterpret_cast<const double*>(stage_raw) + threadIdx.x;
+    for (int t = 0; t < n; ++t) bp[(int64_t)(y_row0 + t) * C] = cascade<kExact, 0, kMaxSec>(q, sp[t * 32], z0, z1);
+  } else if (xf != nullptr) {
+    const float* fp = xf + (int64_t)c * n;
+    for (int t = 0; t < n; ++t) bp[(int64_t)(y_row0 + t) * C] = cascade<kExact, 0, kMaxSec>(q, (double)fp[t], z0, z1);
+  } else {
+    for (int t = 0; t < n; ++t)
+      bp[(int64_t)(y_row0 + t) * C] = cascade<kExact, 0, kMaxSec>(q, xp[(int64_t)t * ldx], z0, z1);
+  }
 #pragma unroll
   for (int s = 0; s < kMaxSec; ++s)
     if (s < q.ns) {
@@ -144,11 +175,143 @@ __global__ void __launch_bounds__(32) k_stream_push(const __grid_constant__ Casc
       const double v = bp[(int64_t)r * C];
       acc = __dadd_rn(acc, __dmul_rn(v, v));
     }
-    out[(int64_t)w * ldo + c] = feature(acc, (double)L, eps, zs, m, sd);
+    const double f = feature(acc, (double)L, eps, zs, m, sd);
+    out[(int64_t)w * ldo + c] = f;
+    if (out_f32 != nullptr) out_f32[(int64_t)w * C + c] = (float)f;
   }
   const int src = rows_total - overlap;
-  if (src > 0)
-    for (int r = 0; r < overlap; ++r) bp[(int64_t)r * C] = bp[(int64_t)(src + r) * C];  // src > dst: forward is safe
+  if (src > 0) {
+    // src > dst: forward is safe.  Batches of 8 rows: the 8 loads of a batch are independent (all issued before the first
+    // store), where the row-by-row form is one dependent L2 round trip per row (the ranges overlap, so the compiler must
+    // order every load after the previous store): 40 rows cost ~14 us of a 20 us kernel that way.
+    int r = 0;
+    for (; r + 8 <= overlap; r += 8) {
+      double v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = bp[(int64_t)(src + r + k) * C];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) bp[(int64_t)(r + k) * C] = v[k];
+    }
+    for (; r < overlap; ++r) bp[(int64_t)r * C] = bp[(int64_t)(src + r) * C];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K-stream-sys: k_stream_push for small packets (rows_total + n <= kStreamFastRows), the same arithmetic bit for bit,
+// laid out for LATENCY instead of one thread per channel:
+//   * a warp owns 2 channels; lane = (channel, section): the 16 biquad sections of a channel sit in 16 lanes and hand
+//     their output to the next lane with a shuffle (a systolic array: section s works on sample k - s at step k).  A
+//     10-sample packet takes 25 steps of ONE section update each instead of 160 dependent section updates per thread
+//     (k_stream_push: 47 k cycles = 24 us per packet under ncu, almost all of it dependent-issue stalls of a lone warp);
+//   * the warp's slice of the frame buffer and of the packet lives in shared memory for the call; every global access
+//     belongs to one of three independent bursts: (1) state, remainder rows and packet in, (2) frames out, (3) new
+//     remainder and state out;
+//   * frame w of a channel is summed in row order (like hga_optimized.pyx:8-24) by lane w % 16 of that channel.
+//   IN = 0: x is float64 (n, ldx) row-major;  IN = 1: x is the float32 [C][n] channel-major payload of a wire packet.
+// x / out may be mapped host memory (zero-copy packets).  Dynamic shared memory: kSysWarps * (rows_total + n) * 16 bytes.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kStreamFastRows = 192;
+constexpr int kSysWarps = 4;
+template <int IN>
+__global__ void __launch_bounds__(32 * kSysWarps) k_stream_push_sys(const __grid_constant__ Cascade q, const void* __restrict__ xin, int64_t ldx,
+                                                                    int n, int C, double* __restrict__ state, double* __restrict__ buf,
+                                                                    int y_row0, int zero_rows, int rows_total, int overlap, int n_frames,
+                                                                    int L, int hop, double eps, const double* __restrict__ mu,
+                                                                    const double* __restrict__ sigma, double* __restrict__ out,
+                                                                    int64_t ldo, float* __restrict__ out_f32) {
+  extern __shared__ __align__(16) double ssm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s = lane & 15, chl = lane >> 4;
+  const int cbase = (blockIdx.x * kSysWarps + warp) * 2, c = cbase + chl;
+  if (cbase >= C) return;                                   // whole warp out of range
+  const bool live = c < C;
+  double* fb = ssm + (size_t)warp * (rows_total + n) * 2;   // [rows_total][2] frame rows of the warp's two channels
+  double* xs = fb + rows_total * 2;                         // [n][2] the packet's samples
+  const int ns = q.ns;
+  const bool sec = s < ns;
+  // ---- burst 1
+  double b0 = 0.0, b1 = 0.0, b2 = 0.0, a1 = 0.0, a2 = 0.0, z0 = 0.0, z1 = 0.0;
+  if (sec) {
+    b0 = q.b0[s]; b1 = q.b1[s]; b2 = q.b2[s]; a1 = q.a1[s]; a2 = q.a2[s];
+    if (live) {
+      z0 = state[(int64_t)(2 * s) * C + c];
+      z1 = state[(int64_t)(2 * s + 1) * C + c];
+    }
+  }
+  for (int i = lane; i < 2 * n; i += 32) {
+    const int ch = i / n, t = i - ch * n, cc = cbase + ch;
+    double v = 0.0;
+    if (cc < C) v = IN == 1 ? (double)static_cast<const float*>(xin)[(int64_t)cc * n + t] : static_cast<const double*>(xin)[(int64_t)t * ldx + cc];
+    xs[t * 2 + ch] = v;
+  }
+  for (int i = lane; i < 2 * y_row0; i += 32) {
+    const int r = i >> 1, cc = cbase + (i & 1);
+    fb[i] = (r >= zero_rows && cc < C) ? buf[(int64_t)r * C + cc] : 0.0;
+  }
+  __syncwarp();
+  // ---- the cascade: section s takes sample k - s at step k (reference operation order, every product and sum rounded)
+  double ylast = 0.0;
+  const int nsteps = n + ns - 1;
+  for (int k = 0; k < nsteps; ++k) {
+    double xi = __shfl_up_sync(0xffffffffu, ylast, 1, 16);
+    const int t = k - s;
+    if (s == 0 && k < n) xi = xs[k * 2 + chl];
+    if (sec && t >= 0 && t < n) {
+      const double y = __dadd_rn(__dmul_rn(b0, xi), z0);
+      z0 = __dadd_rn(__dsub_rn(__dmul_rn(b1, xi), __dmul_rn(a1, y)), z1);
+      z1 = __dsub_rn(__dmul_rn(b2, xi), __dmul_rn(a2, y));
+      ylast = y;
+      if (s == ns - 1) fb[(y_row0 + t) * 2 + chl] = y;
+    }
+  }
+  __syncwarp();
+  // ---- burst 2: frames
+  if (live) {
+    const bool zs = mu != nullptr;
+    const double m = zs ? mu[c] : 0.0, sd = zs ? sigma[c] : 1.0;
+    for (int w = s; w < n_frames; w += 16) {
+      double acc = 0.0;
+      const int a = w * hop;
+      for (int r = a; r < a + L; ++r) {
+        const double v = fb[r * 2 + chl];
+        acc = __dadd_rn(acc, __dmul_rn(v, v));
+      }
+      const double f = feature(acc, (double)L, eps, zs, m, sd);
+      out[(int64_t)w * ldo + c] = f;
+      if (out_f32 != nullptr) out_f32[(int64_t)w * C + c] = (float)f;
+    }
+  }
+  // ---- burst 3: new remainder (the last `overlap` rows) and filter state
+  const int src_row = rows_total - overlap;
+  if (src_row >= 0)
+    for (int i = lane; i < 2 * overlap; i += 32) {
+      const int r = i >> 1, ch = i & 1, cc = cbase + ch;
+      if (cc < C) buf[(int64_t)r * C + cc] = fb[(src_row + r) * 2 + ch];
+    }
+  if (live && sec) {
+    state[(int64_t)(2 * s) * C + c] = z0;
+    state[(int64_t)(2 * s + 1) * C + c] = z1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K-packet: payload of a wire packet, float32 [C][n] channel-major -> float64 (n, C) row-major (ZMQConnector.
+// interpret_bytes, local/units.py:78-82).  A 32 x 32 tile through shared memory: coalesced reads along n, coalesced
+// writes along C.  Bound: HBM / launch latency (a packet is 5 KB).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_packet_rows(const float* __restrict__ p, int C, int n, double* __restrict__ x, int64_t ldx) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int c0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+  for (int k = ty; k < 32; k += 8) {
+    const int c = c0 + k, t = t0 + tx;
+    tile[k][tx] = (c < C && t < n) ? p[(int64_t)c * n + t] : 0.f;
+  }
+  __syncthreads();
+  for (int k = ty; k < 32; k += 8) {
+    const int t = t0 + k, c = c0 + tx;
+    if (t < n && c < C) x[(int64_t)t * ldx + c] = (double)tile[tx][k];
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------

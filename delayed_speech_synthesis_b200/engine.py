@@ -191,11 +191,46 @@ class HgaEngine:
             raise ValueError(f"expected {self.n_channels} channels, got {x.shape[1]}")
         frames = self.stream_frames(x.shape[0])
         out = np.empty((max(frames, 1), self.n_channels), dtype=np.float64)[:frames]
-        mu_h, sg_h = _musigma_host(mu, sigma, self.n_channels)
+        mu_h, sg_h = self._musigma_cached(mu, sigma)
         check(self._lib.hga_stream_push_host(self._h, x.ctypes.data, x.shape[0], x.strides[0] // 8,
                                              mu_h.ctypes.data if mu_h is not None else None,
                                              sg_h.ctypes.data if sg_h is not None else None,
                                              out.ctypes.data, self.n_channels, C.byref(nf)))
+        assert nf.value == frames
+        return out
+
+    def _musigma_cached(self, mu, sigma):
+        """`_musigma_host`, skipped when the caller passes the same two objects as last time (a streaming extractor hands
+        over its ZScoreNormalization's arrays on every packet; the C side compares the contents anyway)."""
+        key = getattr(self, "_ms_key", None)
+        if key is not None and key[0] is mu and key[1] is sigma:
+            return self._ms_val
+        val = _musigma_host(mu, sigma, self.n_channels)
+        self._ms_key, self._ms_val = (mu, sigma), val
+        return val
+
+    def push_packet(self, packet, mu=None, sigma=None, out_f32=None):
+        """`interpret_bytes` + `extract_features` for one wire packet (local/units.py:78-82,145-161): bytes of the
+        '=BBB HH' header + float32 channel-major payload -> (F, C) float64 numpy frames.  The kernel reads the payload
+        as it lies; no (n, C) float64 copy is made.  out_f32: optional CUDA float32 (>= F, C) tensor that also
+        receives the frames (for a consumer on the same GPU)."""
+        raw = bytes(packet)
+        n_ch, n_s = C.c_int32(0), C.c_int32(0)
+        check(self._lib.hga_packet_header(raw, len(raw), C.byref(n_ch), C.byref(n_s)))
+        frames = self.stream_frames(n_s.value) if n_s.value > 0 else 0
+        out = np.empty((max(frames, 1), self.n_channels), dtype=np.float64)[:frames]
+        mu_h, sg_h = self._musigma_cached(mu, sigma)
+        f32_ptr = None
+        if out_f32 is not None:
+            torch = _torch()
+            if not (isinstance(out_f32, torch.Tensor) and out_f32.is_cuda and out_f32.dtype == torch.float32 and out_f32.is_contiguous()
+                    and out_f32.dim() == 2 and out_f32.shape[1] == self.n_channels and out_f32.shape[0] >= frames):
+                raise ValueError("out_f32 must be a contiguous CUDA float32 (>= F, C) tensor")
+            f32_ptr = out_f32.data_ptr()
+        nf = C.c_int64(0)
+        check(self._lib.hga_stream_push_packet(self._h, raw, len(raw), mu_h.ctypes.data if mu_h is not None else None,
+                                               sg_h.ctypes.data if sg_h is not None else None, out.ctypes.data, self.n_channels,
+                                               f32_ptr, C.byref(nf)))
         assert nf.value == frames
         return out
 

@@ -135,6 +135,22 @@ class HighGammaExtractor:
                 return ("numpy", cmap.apply(data))
         return cmap.apply(data)
 
+    def extract_features_packet(self, packet: bytes):
+        """`ZMQConnector.interpret_bytes` (:78-82) followed by `extract_features` (:145-161) for one wire packet.  Without
+        pre-transforms the extraction kernel reads the packet's float32 channel-major payload directly; with them the
+        packet is decoded on the device and the (n, C_in) tensor takes the usual route."""
+        if self.pre_transform is None and self._post_map is None and (self.post_transform is None or self._fused_zscore is not None):
+            mu = sigma = None
+            if self._fused_zscore is not None:
+                mu, sigma = self._fused_zscore.channel_means, self._fused_zscore.channel_stds
+            return self._engine.push_packet(packet, mu, sigma)
+        from . import wire
+        n_ch, _ = wire.packet_shape(packet)
+        spec = transforms.fold(self._pre_list, n_ch) if self._pre_list else None
+        on_device = spec is not None and spec.c_out == self.nb_electrodes      # else the user's callables want ndarrays
+        out = self.extract_features(wire.interpret_bytes(packet, self._engine.device, as_numpy=not on_device))
+        return out.cpu().numpy() if isinstance(out, _torch().Tensor) else out
+
     def extract_features(self, data):                                              # :145-161
         as_numpy = False
         if self.pre_transform is not None:

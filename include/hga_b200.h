@@ -124,6 +124,21 @@ int hga_stream_push(hga_handle* h, const double* x_dev, int64_t n, int64_t ldx, 
 int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t n, int64_t ldx, const double* mu_host,
                          const double* sigma_host, double* out_host, int64_t ldo, int64_t* n_frames);
 
+/* ---- wire packets at the streaming seam ------------------------------------------------------- */
+/* A packet is what ZMQConnector.process receives (local/units.py:78-93) and development_amplifier.py:14-25 packs:
+ * struct '=BBB HH' (descriptor, supplement, dtype, n_channels, n_samples; 7 bytes) + n_channels * n_samples float32,
+ * channel-major.  hga_packet_header parses and validates it on the host (the payload length must match the header). */
+int hga_packet_header(const void* packet_host, int64_t nbytes, int32_t* n_channels, int32_t* n_samples);
+/* ZMQConnector.interpret_bytes (local/units.py:78-82) with the result on the device: float32 [C][n] -> float64 (n, C)
+ * row-major at x_dev (leading dimension ldx >= C).  Enqueued on `stream`; the packet may be reused on return. */
+int hga_packet_decode(int32_t device, const void* packet_host, int64_t nbytes, double* x_dev, int64_t ldx, void* stream);
+/* interpret_bytes + HighGammaExtractor.extract_features (local/units.py:78-82,145-161) for one packet on a long-lived
+ * extractor: the kernel reads the float32 channel-major payload directly.  out_host receives the float64 frames like
+ * hga_stream_push_host; out_f32_dev (device, (n_frames, C) float32, or NULL) additionally receives them as float32 for
+ * a consumer on the same GPU (the nVAD's `.float().to(device)`, local/units.py:433).  Packets of 1..1024 samples. */
+int hga_stream_push_packet(hga_handle* h, const void* packet_host, int64_t nbytes, const double* mu_host,
+                           const double* sigma_host, double* out_host, int64_t ldo, float* out_f32_dev, int64_t* n_frames);
+
 /* Streaming state, in the reference's own shapes: hg_state/fh_state (n_sections, 2, C) as local/units.py:131-132,
  * remainder (frame_len - hop, C) and the first_frame flag as hga_optimized.pyx:78-88.  HOST buffers; NULL = skip. */
 int hga_get_state(hga_handle* h, double* hg_state, double* fh_state, double* remainder, int32_t* first_frame);

@@ -361,3 +361,25 @@ def bad_channel_correction(data: np.ndarray, patches) -> np.ndarray:
     for loc, neigh in patches:
         out[:, loc] = np.mean(data[:, neigh], axis=1).reshape((len(data), -1))
     return out
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Wire packets at the streaming seam.  Pinned against the reference's own ZMQConnector.interpret_bytes
+# and BCI2000Package.pack, executed by tests/golden/make_golden.py (tests/golden/packets.npz).
+# ----------------------------------------------------------------------------------------------------------------------
+def interpret_bytes(data: bytes) -> np.ndarray:
+    """ZMQConnector.interpret_bytes (local/units.py:78-82): '=BBB HH' header, float32 [n_channels][n_samples] payload ->
+    (n_samples, n_channels) float64, C order."""
+    import struct
+    header = struct.Struct('=BBB HH')
+    _, _, _, n_channels, n_samples = header.unpack(data[:header.size])
+    array = np.frombuffer(data[header.size:], dtype=np.float32).reshape(n_channels, n_samples)
+    return np.transpose(array).astype(np.float64, order='C', copy=True)
+
+
+def pack_packet(payload: np.ndarray) -> bytes:
+    """BCI2000Package(nb_channels, nb_samples).pack(payload) (development_amplifier.py:14-25): header (4, 1, 2, C, n) and
+    the payload flattened in C order as float32."""
+    import struct
+    payload = np.asarray(payload)
+    return struct.pack('=BBB HH', 4, 1, 2, payload.shape[0], payload.shape[1]) + np.ascontiguousarray(payload, dtype=np.float32).tobytes()

@@ -11,7 +11,9 @@ Pieces executed:
   * scipy.signal.sosfilt / sosfilt_zi / iirfilter (the third-party code the reference calls, local/units.py:124-152);
   * the composition of local/units.py:145-161 written out literally with those pieces;
   * the reference's channel-transform classes (local/common.py), cut out of its AST and executed unmodified
-    (`python tests/golden/make_golden.py transforms` regenerates only transforms.npz).
+    (`python tests/golden/make_golden.py transforms` regenerates only transforms.npz);
+  * the reference's packet code (development_amplifier.py BCI2000Package, local/units.py ZMQConnector.interpret_bytes), cut
+    out of the AST and executed unmodified (`... make_golden.py packets` regenerates only packets.npz).
 """
 from __future__ import annotations
 
@@ -97,7 +99,36 @@ def transforms_golden():
     np.savez(HERE / "transforms.npz", **out)
 
 
+def packets_golden():
+    """The reference's own packet code, cut out of its AST and executed unmodified: BCI2000Package (development_amplifier.py
+    :14-25) packs seeded payloads, ZMQConnector.interpret_bytes (local/units.py:78-82) decodes them (tests/golden/packets.npz)."""
+    import ast
+    import struct
+    import types
+    ns = {"struct": struct, "np": np}
+    for node in ast.parse(Path("/root/reference/development_amplifier.py").read_text()).body:
+        if isinstance(node, ast.ClassDef) and node.name == "BCI2000Package":
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "/root/reference/development_amplifier.py", "exec"), ns)
+    for node in ast.parse(Path("/root/reference/local/units.py").read_text()).body:
+        if isinstance(node, ast.ClassDef) and node.name == "ZMQConnector":
+            fn = next(n for n in node.body if isinstance(n, ast.FunctionDef) and n.name == "interpret_bytes")
+            exec(compile(ast.Module(body=[fn], type_ignores=[]), "/root/reference/local/units.py", "exec"), ns)
+    fake_self = types.SimpleNamespace(STATE=types.SimpleNamespace(header=struct.Struct('=BBB HH')))
+    rng = np.random.Generator(np.random.Philox(key=[20241104, 11]))
+    out = {}
+    for name, (c, n) in {"a": (128, 10), "b": (5, 3), "c": (64, 40), "d": (1, 1)}.items():
+        payload = (rng.standard_normal((c, n)) * 30).astype(np.float32)
+        pkt = ns["BCI2000Package"](c, n).pack(payload)
+        out[f"packet_{name}"] = np.frombuffer(pkt, dtype=np.uint8)
+        out[f"decoded_{name}"] = ns["interpret_bytes"](fake_self, pkt)
+    np.savez(HERE / "packets.npz", **out)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "packets":
+        packets_golden()
+        print("golden written: packets.npz")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "transforms":
         transforms_golden()
         print("golden written: transforms.npz")
@@ -156,6 +187,7 @@ def main():
              stream=np.concatenate(frames), stream_hg_state=hs, stream_fh_state=fh)
     framebuffer_golden()
     transforms_golden()
+    packets_golden()
     print("golden written:", sorted(p.name for p in HERE.glob("*.npz")))
 
 
