@@ -32,3 +32,87 @@ def gather_accumulators(acc, group=None):
 def day_slots(days: Sequence[int]) -> Dict[int, int]:
     """Stable slot index per distinct day label (every rank must derive the same table)."""
     return {d: i for i, d in enumerate(sorted(set(days)))}
+
+
+# ---------------------------------------------------------------------------------------------- per-trial extraction
+def trial_segments(trial_indices, fs: float, n_rows: int, tail: float = 0.04):
+    """The row ranges `FeatureExtractionPipeline.get_features` slices out of a recording (prepare_corpus.py:47-50):
+    `ecog[start:int(stop + tail * fs), :]` per (label, start, stop) trial, clipped to the recording like a numpy slice
+    (trial indices are sample positions, i.e. non-negative)."""
+    segs = []
+    for _, start, stop in trial_indices:
+        a = min(max(int(start), 0), n_rows)
+        b = min(max(int(stop + (tail * fs)), 0), n_rows)
+        segs.append((a, max(a, b)))
+    return segs
+
+
+def extract_trials(ecog, trial_indices, fs: int, nb_electrodes: int, pre_transforms=None, post_transforms=None,
+                   window_length: float = 0.05, window_shift: float = 0.01, l_freq: float = 70, h_freq: float = 170,
+                   tail: float = 0.04, precision: str = "f64", device: Optional[int] = None):
+    """`FeatureExtractionPipeline.get_features` (prepare_corpus.py:42-52) as ONE batched launch (the part
+    that needs no file I/O): every trial is filtered by a fresh extractor (initial state sosfilt_zi, fresh frame buffer),
+    the features of all trials are concatenated.  The reference builds a `HighGammaExtractor` per trial and loops in Python.
+
+    ecog: (T, C_in) float64 ndarray, e.g. `BCI2000MatFile.signals()`.  pre/post transforms as for `HighGammaExtractor`:
+    chains of the reference's selection / CAR / bad-channel objects run as one channel-map kernel over the whole recording
+    (they are row-wise, so slicing before or after is the same); anything else is called per trial like the reference does.
+    Returns a (sum of frames, nb_electrodes) float64 ndarray."""
+    import numpy as np
+    import torch
+
+    from . import transforms
+    from .engine import HgaEngine
+
+    ecog = np.asarray(ecog)
+    if ecog.ndim != 2:
+        raise ValueError(f"expected (T, C) data, got {ecog.shape}")
+    if ecog.dtype != np.float64:
+        ecog = ecog.astype(np.float64)
+    eng = HgaEngine(fs, nb_electrodes, window_length, window_shift, l_freq, h_freq, precision=precision, device=device)
+    dev = eng.device
+    segs = trial_segments(trial_indices, fs, len(ecog), tail)
+    L = eng.frame_len
+    spec = transforms.fold(pre_transforms, ecog.shape[1]) if pre_transforms else None
+    if pre_transforms and (spec is None or spec.c_out != nb_electrodes):
+        # unfoldable chain: the user's callables see each trial slice, exactly as the reference calls them; the results are
+        # laid end to end and become the segment table of the one launch
+        parts = [np.asarray(_compose(pre_transforms)(ecog[a:b])) for a, b in segs]
+        offs = np.concatenate([[0], np.cumsum([len(p) for p in parts])])
+        x = torch.from_numpy(np.ascontiguousarray(np.concatenate(parts) if parts else np.zeros((0, nb_electrodes)), dtype=np.float64)).cuda(dev)
+        segs = [(int(offs[i]), int(offs[i + 1])) for i in range(len(parts))]
+    else:
+        x = torch.from_numpy(np.ascontiguousarray(ecog)).cuda(dev)
+        if spec is not None:
+            x = transforms.ChannelMap(spec, dev).apply(x)
+    if x.shape[1] != nb_electrodes:
+        raise ValueError(f"expected {nb_electrodes} channels after the pre-transforms, got {x.shape[1]}")
+    long_ = [(i, s) for i, s in enumerate(segs) if s[1] - s[0] >= L]
+    feats = [None] * len(segs)
+    if long_:
+        out = eng.extract_offline(x, [s for _, s in long_])
+        rows = np.concatenate([[0], np.cumsum([eng.num_frames(s[1] - s[0]) for _, s in long_])])
+        for k, (i, _) in enumerate(long_):
+            feats[i] = out[int(rows[k]):int(rows[k + 1])]
+    for i, (a, b) in enumerate(segs):
+        if feats[i] is None:  # shorter than one window: a fresh extractor zero-pads it to one frame (frame-buffer case 2)
+            if b - a < 1:
+                feats[i] = x.new_zeros((0, nb_electrodes))
+            else:
+                eng.reset()
+                feats[i] = eng.push(x[a:b].contiguous())
+    res = torch.cat(feats) if feats else x.new_zeros((0, nb_electrodes))
+    if post_transforms:
+        pspec = transforms.fold(post_transforms, nb_electrodes)
+        if pspec is not None and pspec.c_out == nb_electrodes and len(res):
+            res = transforms.ChannelMap(pspec, dev).apply(res.contiguous())
+        else:
+            # the reference applies post-transforms per trial; row-wise callables commute with the concatenation
+            return np.concatenate([np.asarray(_compose(post_transforms)(f.cpu().numpy())) for f in feats]) if feats else res.cpu().numpy()
+    return res.cpu().numpy()
+
+
+def _compose(functions):
+    """`HighGammaExtractor._compose_functions` (local/units.py:134-136)."""
+    from functools import reduce
+    return reduce(lambda f, g: lambda v: g(f(v)), functions, lambda v: v)
