@@ -275,12 +275,12 @@ static int upload_log_table() {
 struct PipeShape {
   int ver, S, TB;
 };
-// Default: k_hga_pipe2 with 4 filter warps x 4 sections and 40-row tiles, one CTA per SM (measured best for both
-// precisions on K2, profiles/r01_pipe2_sweep.txt).  HGA_B200_PIPE_V=1 selects the first-generation kernel (k_hga_pipe,
+// Default: k_hga_pipe2 with 4 filter warps x 4 sections, one CTA per SM; 80-row tiles with 2-deep rings in float64 mode
+// (K2: 40 rows 183 G, 60 rows 196 G, 80 rows 201 G channel-samples/s: a tile boundary costs ~300 cycles per warp), 40-row
+// tiles in float32 mode (its 20 KB x tiles leave no room for more).  HGA_B200_PIPE_V=1 selects the first-generation kernel (k_hga_pipe,
 // S in {2, 4}); HGA_B200_PIPE_S / HGA_B200_PIPE_TB pick the other compiled shapes (A/B runs).
 static PipeShape pipe_shape(bool f32 = false) {
-  (void)f32;
-  PipeShape p{2, 4, 40};
+  PipeShape p{2, 4, f32 ? 40 : 80};
   if (const char* e = getenv("HGA_B200_PIPE_V")) p.ver = atoi(e) == 1 ? 1 : 2;
   if (p.ver == 1) { p.S = 4; p.TB = 40; }
   if (const char* e = getenv("HGA_B200_PIPE_S")) p.S = atoi(e);
@@ -291,7 +291,8 @@ static PipeShape pipe_shape(bool f32 = false) {
   } else {
     if (p.S != 4 && p.S != 8) p.S = 4;
     if (p.S == 8) p.TB = 20;
-    else if (p.TB != 20 && p.TB != 40) p.TB = 40;
+    else if (p.TB != 20 && p.TB != 40 && !((p.TB == 60 || p.TB == 70 || p.TB == 80) && !f32)) p.TB = 40;  // > 40-row tiles: float64 only
+    // (float32 mode: 60-row tiles fit with 2-deep rings but that kernel shape faults on the device; not debugged, not offered)
   }
   return p;
 }
@@ -345,8 +346,8 @@ template <typename T, int S, int TB, int HOP>
 static int pipe2_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
   constexpr int NS = kMaxSec / S;
   constexpr unsigned kHalf = (1u << (NS / 2)) - 1u;  // form56: the first NS/2 sections of every warp are A sections
-  if (S == 4 && TB == 40 && pc.amask != 0 && pipe2_nf(PipeTraits<T>::CPL == 2) == 8)
-    return pipe2_launch_am<T, S, TB, HOP, kHalf, (S == 4 && TB == 40 ? 8 : 4)>(q, pc, a, tm, st, occ);
+  if (S == 4 && (TB == 40 || TB == 60) && pc.amask != 0 && pipe2_nf(PipeTraits<T>::CPL == 2) == 8)
+    return pipe2_launch_am<T, S, TB, HOP, kHalf, (S == 4 && (TB == 40 || TB == 60) ? 8 : 4)>(q, pc, a, tm, st, occ);
   if (pc.amask != 0) return pipe2_launch_am<T, S, TB, HOP, kHalf>(q, pc, a, tm, st, occ);
   return pipe2_launch_am<T, S, TB, HOP, 0u>(q, pc, a, tm, st, occ);
 }
@@ -358,10 +359,19 @@ static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs&
     if (hop == 10) {
       if (p.S == 8) return pipe2_launch_t<T, 8, 20, 10>(q, pc, a, tm, st, occ);
       if (p.TB == 20) return pipe2_launch_t<T, 4, 20, 10>(q, pc, a, tm, st, occ);
+      if constexpr (PipeTraits<T>::CPL == 1) {
+        if (p.TB == 60) return pipe2_launch_t<T, 4, 60, 10>(q, pc, a, tm, st, occ);
+        if (p.TB == 70) return pipe2_launch_t<T, 4, 70, 10>(q, pc, a, tm, st, occ);
+        if (p.TB == 80) return pipe2_launch_t<T, 4, 80, 10>(q, pc, a, tm, st, occ);
+      }
       return pipe2_launch_t<T, 4, 40, 10>(q, pc, a, tm, st, occ);
     }
     if (p.S == 8) return pipe2_launch_t<T, 8, 20, 20>(q, pc, a, tm, st, occ);
     if (p.TB == 20) return pipe2_launch_t<T, 4, 20, 20>(q, pc, a, tm, st, occ);
+    if constexpr (PipeTraits<T>::CPL == 1) {
+      if (p.TB >= 80) return pipe2_launch_t<T, 4, 80, 20>(q, pc, a, tm, st, occ);
+      if (p.TB >= 60) return pipe2_launch_t<T, 4, 60, 20>(q, pc, a, tm, st, occ);
+    }
     return pipe2_launch_t<T, 4, 40, 20>(q, pc, a, tm, st, occ);
   }
   if (hop == 10) {
@@ -394,7 +404,8 @@ static int launch_pipe(const Cascade& q, const PipeOperands& po, int precision, 
   const cuuint64_t dims[2] = {(cuuint64_t)a.C, (cuuint64_t)(a.x_row_hi - a.x_row_lo)};
   const cuuint64_t strides[1] = {(cuuint64_t)a.ldx * 8};
   const PipeShape p = pipe_shape(precision == HGA_PREC_F32);
-  const cuuint32_t box[2] = {precision == HGA_PREC_F32 ? 64u : 32u, (cuuint32_t)p.TB};
+  const int tb_eff = (a.hop == 20 && p.ver == 2 && p.TB == 70) ? 60 : p.TB;  // 70 rows are not a whole number of 20-row hop blocks
+  const cuuint32_t box[2] = {precision == HGA_PREC_F32 ? 64u : 32u, (cuuint32_t)tb_eff};
   const cuuint32_t es[2] = {1, 1};
   void* base = (void*)(a.x + a.x_row_lo * a.ldx);
   const CUresult r = encode_tiled_fn()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,

@@ -61,12 +61,15 @@ __device__ __forceinline__ double tab_log(double x, const double* __restrict__ t
 template <int S, int TB, typename T>
 struct Pipe2Smem {
   static constexpr int CPL = PipeTraits<T>::CPL;
-  static constexpr int NX = PipeTraits<T>::CPL == 1 ? 4 : 3;  // TMA ring depth (float32 mode: 20 KB tiles, no room for a 4th)
+  // Ring depths shrink as the tiles grow (227 KB of shared memory): a tile boundary costs ~300 cycles per filter warp
+  // (two mbarrier waits, two arrivals, the load prologue, hand-off jitter), so long tiles with shallow rings beat short
+  // tiles with deep rings (K2 float64: 40 rows 183 G, 60 rows 196 G, 80 rows 201 G channel-samples/s).
+  static constexpr int NX = PipeTraits<T>::CPL == 1 ? (TB >= 80 ? 2 : TB >= 70 ? 3 : 4) : (TB > 40 ? 2 : 3);  // TMA ring depth
 #ifndef HGA_PIPE2_NB64
 #define HGA_PIPE2_NB64 3
 #endif
-  static constexpr int NB = PipeTraits<T>::CPL == 1 ? HGA_PIPE2_NB64 : 2;  // buffers per internal link
-  static constexpr int NBY = 4;   // y tiles (filter warp S-1 -> framing warps)
+  static constexpr int NB = (PipeTraits<T>::CPL == 1 && TB <= 40) ? HGA_PIPE2_NB64 : 2;  // buffers per internal link
+  static constexpr int NBY = TB <= 40 ? 4 : (TB >= 80 || PipeTraits<T>::CPL == 2) ? 2 : 3;   // y tiles (filter warp S-1 -> framing warps)
   static constexpr int kBsRing = TB / 10 >= 4 ? 32 : 16;  // hop-block sums kept (framing warps may be two tiles apart)
   static constexpr int NBS = 4;   // block-sum hand-off barriers (phase A of tile m -> phase B of tile m)
   static constexpr int NBC = NX;  // float32 mode: converted x tiles (framing warps -> filter warp 0)
@@ -75,7 +78,7 @@ struct Pipe2Smem {
   static constexpr int NL = S - 1;  // links between filter warps
   static constexpr size_t link_bytes = (size_t)NL * NB * TB * 32 * sizeof(T);
   static constexpr size_t y_bytes = (size_t)NBY * TB * 32 * sizeof(T);
-  static constexpr size_t bs_bytes = (size_t)kBsRing * 32 * CPL * 8;
+  static constexpr size_t bs_bytes = (size_t)kBsRing * 32 * CPL * (CPL == 2 ? 4 : 8);  // float32 mode keeps its block sums in float32
   static constexpr size_t tab_bytes = 256 * 8;  // log table (kLogTabN x {1/c, -log(1/c)})
   static constexpr size_t c_off = x_bytes, link_off = c_off + c_bytes, y_off = link_off + link_bytes, bs_off = y_off + y_bytes,
                           tab_off = bs_off + bs_bytes, bar_off = tab_off + tab_bytes;
@@ -465,9 +468,10 @@ __global__ void __launch_bounds__(32 * (S + NF + 1), 1) k_hga_pipe2(const __grid
                 acc0 = fmaf(v[i], v[i], acc0);
                 acc1 = fmaf(v[i + 1], v[i + 1], acc1);
               }
-              bsum = (double)(acc0 + acc1);
+              reinterpret_cast<float*>(bs)[((blk_begin + brel) & (SM::kBsRing - 1)) * CW + lane + 32 * p] = acc0 + acc1;
+              bsum = 0.0;
             }
-            bs[((blk_begin + brel) & (SM::kBsRing - 1)) * CW + lane + 32 * p] = bsum;
+            if (CPL == 1) bs[((blk_begin + brel) & (SM::kBsRing - 1)) * CW + lane + 32 * p] = bsum;
           }
         }
       }
@@ -494,7 +498,10 @@ __global__ void __launch_bounds__(32 * (S + NF + 1), 1) k_hga_pipe2(const __grid
           if (brel >= 0 && tb >= wk.t_acc + (int64_t)(kPipeNB - 1) * HOP && tb + HOP <= wk.t_end) {
             double vv[kPipeNB];
 #pragma unroll
-            for (int k = 0; k < kPipeNB; ++k) vv[k] = bs[((blk - (kPipeNB - 1) + k) & (SM::kBsRing - 1)) * CW + lane + 32 * p];
+            for (int k = 0; k < kPipeNB; ++k) {
+              const int bi = ((blk - (kPipeNB - 1) + k) & (SM::kBsRing - 1)) * CW + lane + 32 * p;
+              vv[k] = CPL == 1 ? bs[bi] : (double)reinterpret_cast<const float*>(bs)[bi];  // widened here: window sums, log, z-score are float64
+            }
             double sacc = vv[0];
 #pragma unroll
             for (int k = 1; k < kPipeNB; ++k) sacc += vv[k];  // oldest block first, like the sequential kernel

@@ -1,0 +1,4 @@
+B="python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline --no-stream"
+for tb in 60 70 80; do for w in k2 k4; do
+echo "== TB=$tb $w"; HGA_B200_PIPE_TB=$tb timeout 300 $B --workload $w 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['dtype'], d['value']/1e9, d['ms_per_step'], d['roofline']['frac'])"
+done; done
