@@ -157,7 +157,31 @@ def test_offline_time_chunked_long(torch):
     assert a <= TOL_F64, (a, r)
 
 
-@pytest.mark.parametrize("variant,S,TB", [("0", "4", "40"), ("1", "4", "40"), ("1", "2", "40")])
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_offline_full_size_k2_windows(precision, torch):
+    """BASELINE config 2 at full size (128 ch x 1 h @ 1 kHz, 3.69 GB, generated on the device): the 60 s prefix against a
+    fresh-start oracle, and 1 s windows at seeded positions anywhere in the hour against an oracle run that starts 14 s
+    earlier (its own start transient has decayed by 1e-14 by then).  Checks the time-chunking at the size the bench runs."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, C = 1000, 3_600_000, 128
+    tol = TOL_F64 if precision == "f64" else TOL_F32
+    g = torch.Generator(device="cuda").manual_seed(20241104)
+    x = torch.randn((T, C), dtype=torch.float64, device="cuda", generator=g)
+    feats = HgaEngine(fs, C, precision=precision).extract_offline(x)
+    assert feats.shape == ((T - 50) // 10 + 1, C)
+    ref = _oracle_offline(x[:60000].cpu().numpy(), fs)
+    assert _err(feats[:len(ref)].cpu().numpy(), ref)[0] <= tol
+    rng = np.random.Generator(np.random.Philox(key=[20241104, 99]))
+    lead, span = 14000, 1000
+    for t0 in sorted(int(v) * 10 for v in rng.integers(lead // 10, (T - span) // 10, size=6)) + [T - span]:
+        ref = _oracle_offline(x[t0 - lead:t0 + span].cpu().numpy(), fs)      # frame k of the slice = frame (t0 - lead) / 10 + k
+        k0 = lead // 10
+        got = feats[t0 // 10:t0 // 10 + (span - 50) // 10 + 1].cpu().numpy()
+        assert _err(got, ref[k0:k0 + len(got)])[0] <= tol, t0
+    assert bool(torch.isfinite(feats).all())
+
+
+@pytest.mark.parametrize("variant,S,TB", [("0", "4", "40"), ("1", "4", "40"), ("1", "2", "40"), ("1", "4", "20"), ("1", "4", "60"), ("1", "4", "80"), ("1", "8", "20")])
 def test_offline_kernel_variants_agree(variant, S, TB, torch, monkeypatch):
     """The thread-sequential and the section-pipelined kernels (every warps-per-item / tile shape) against the oracle:
     ragged segments (partial tiles, lengths that are not hop multiples), C not a multiple of 32, z-score."""
@@ -174,6 +198,20 @@ def test_offline_kernel_variants_agree(variant, S, TB, torch, monkeypatch):
     got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda(), segs, mu, sigma).cpu().numpy()
     assert got.shape == ref.shape
     assert _err(got, ref)[0] <= 5 * TOL_F64
+
+
+def test_offline_caller_section_form_agrees(torch, monkeypatch):
+    """HGA_B200_FORM=64: the pipelined kernel with every section in the caller's [1, b1, 1] form and order (what a cascade
+    that cannot be re-paired into [1, 0, -1] sections gets) against the oracle, both precisions."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    monkeypatch.setenv("HGA_B200_FORM", "64")
+    fs, C = 1000, 128
+    x = O.synthetic_ecog(150000, C, fs, "ecog", session=13)
+    segs = [(0, 70000), (70000, 150000)]
+    ref = _oracle_offline(x, fs, segments=segs)
+    xd = torch.from_numpy(x).cuda()
+    assert _err(HgaEngine(fs, C, precision="f64").extract_offline(xd, segs).cpu().numpy(), ref)[0] <= TOL_F64
+    assert _err(HgaEngine(fs, C, precision="f32").extract_offline(xd, segs).cpu().numpy(), ref)[0] <= TOL_F32
 
 
 @pytest.mark.parametrize("kind", ["white", "ecog"])
