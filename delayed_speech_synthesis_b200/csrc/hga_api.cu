@@ -446,8 +446,8 @@ static int64_t pipe_item_slots(const Cascade& q, const PipeOperands& po, int pre
   CUtensorMap tm{};
   if ((precision == HGA_PREC_F32 ? pipe_dispatch<f32x2>(q, pc, a, hop, tm, nullptr, &occ) : pipe_dispatch<double>(q, pc, a, hop, tm, nullptr, &occ)) != HGA_OK) occ = 1;
   if (const char* e = getenv("HGA_B200_PIPE_OCC")) occ = std::max(1, std::min(occ, atoi(e)));
-  const int cw = precision == HGA_PREC_F32 ? 64 : 32;
-  return std::max<int64_t>(1, (int64_t)n_sm * std::max(1, occ) / ((C + cw - 1) / cw));
+  (void)C;
+  return std::max<int64_t>(1, (int64_t)n_sm * std::max(1, occ));  // resident CTAs of the whole device
 }
 
 // ------------------------------------------------------------------------------------------------ the handle
@@ -602,13 +602,14 @@ extern "C" int64_t hga_num_frames(const hga_handle* h, int64_t rows) {
 // ------------------------------------------------------------------------------------------------ offline path
 // Build the time-chunk work list.  Cost model: items run `slots` warps at a time, each costing (chunk + warm-up)
 // samples; pick the chunk length that minimises waves * (chunk + warmup).
+// slots_ctas: CTAs (work item x channel group) the device runs at a time; groups: channel groups per work item.
 static void plan_chunks(hga_handle* h, int n_seg, const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
-                        int64_t slots_items, bool allow_chunking) {
+                        int64_t slots_ctas, int64_t groups, bool allow_chunking) {
   const int hop = h->cfg.hop, K = h->warmup, nb = h->nb;
   int64_t total = 0, maxT = 0;
   for (int i = 0; i < n_seg; ++i) { total += seg_len[i]; maxT = std::max(maxT, seg_len[i]); }
   int64_t best_Lc = (maxT + hop - 1) / hop * hop;
-  if (allow_chunking && slots_items > 0) {
+  if (allow_chunking && slots_ctas > 0) {
     double best = 1e300;
     const int64_t min_Lc = std::max<int64_t>((int64_t)h->cfg.frame_len * 4, 64 * hop);
     for (int64_t n = 1; n <= 1 << 20; n = n < 64 ? n + 1 : n + n / 16) {
@@ -616,7 +617,8 @@ static void plan_chunks(hga_handle* h, int n_seg, const int64_t* seg_start, cons
       if (Lc < min_Lc) break;
       int64_t items = 0;
       for (int i = 0; i < n_seg; ++i) items += (seg_len[i] + Lc - 1) / Lc;
-      const int64_t waves = (items + slots_items - 1) / slots_items;
+      const int64_t waves = (items * groups + slots_ctas - 1) / slots_ctas;  // e.g. K4 float64: 9 chunks x 32 groups = 288 CTAs = 2 waves
+                                                                              // of 148 beat 4 x 32 = 128 CTAs in 1 wave (86 % of the SMs)
       const double per = (double)std::min(Lc, maxT) + (items > n_seg ? (double)K : 0.0);
       const double cost = waves * per;
       if (cost < best * 0.999) { best = cost; best_Lc = Lc; }
@@ -701,9 +703,13 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
   if (key != h->plan_key || variant != h->plan_variant) {
     const int cg = (C + 31) / 32;
     int64_t slots = 0;
-    if (variant == 0) slots = std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
-    else if (variant == 1) slots = pipe_item_slots(h->q, h->po, h->cfg.precision, h->cfg.hop, h->n_sm, C);
-    plan_chunks(h, n_seg, seg_start, seg_len, out_row, slots, fused);
+    int64_t groups = cg;
+    if (variant == 0) slots = std::max<int64_t>(1, (int64_t)h->n_sm * 12);
+    else if (variant == 1) {
+      slots = pipe_item_slots(h->q, h->po, h->cfg.precision, h->cfg.hop, h->n_sm, C);
+      groups = h->cfg.precision == HGA_PREC_F32 ? (C + 63) / 64 : cg;
+    }
+    plan_chunks(h, n_seg, seg_start, seg_len, out_row, slots, groups, fused);
     if ((rc = upload_plan(h, st))) return rc;
     h->plan_key = key;
     h->plan_variant = variant;
@@ -1300,8 +1306,9 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
     if (variant == -3) return fail(HGA_ERR_UNSUPPORTED, "f32 precision needs the standard 8+8-section unit-gain cascade and hop 10 or 20");
     if (key != h->plan_key || variant != h->plan_variant) {
       const int cg = (C + 31) / 32;
-      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->po, h->cfg.precision, h->cfg.hop, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12 / cg);
-      plan_chunks(h, n_segments, seg_start, seg_len, out_row, slots, true);
+      const int64_t slots = variant == 1 ? pipe_item_slots(h->q, h->po, h->cfg.precision, h->cfg.hop, h->n_sm, C) : std::max<int64_t>(1, (int64_t)h->n_sm * 12);
+      const int64_t groups = (variant == 1 && h->cfg.precision == HGA_PREC_F32) ? (C + 63) / 64 : cg;
+      plan_chunks(h, n_segments, seg_start, seg_len, out_row, slots, groups, true);
       if ((rc = upload_plan(h, sk))) return rc;
       h->plan_key = key;
       h->plan_variant = variant;
