@@ -1167,7 +1167,7 @@ extern "C" int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t
 // ------------------------------------------------------------------------------------------------ channel maps
 // Gather / common-average-reference / bad-channel patch along the channel axis (hga_kernels_pre.cuh).
 struct hga_chanmap {
-  int device = 0, c_in = 0, c_out = 0, n_groups = 0, n_sm = 0;
+  int device = 0, c_in = 0, c_out = 0, n_groups = 0, n_idx = 0, n_sm = 0;
   DevBuf tab;  // sel | grp | gptr | gidx (int32) followed by alpha | beta (double)
   const int32_t *sel = nullptr, *grp = nullptr, *gptr = nullptr, *gidx = nullptr;
   const double *alpha = nullptr, *beta = nullptr;
@@ -1193,7 +1193,7 @@ extern "C" int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, c
     if (gidx[k] < 0 || gidx[k] >= c_in) return fail(HGA_ERR_INVALID, "group column %d outside [0, %d)", gidx[k], c_in);
   CU(cudaSetDevice(device));
   hga_chanmap* m = new hga_chanmap();
-  m->device = device; m->c_in = c_in; m->c_out = c_out; m->n_groups = n_groups;
+  m->device = device; m->c_in = c_in; m->c_out = c_out; m->n_groups = n_groups; m->n_idx = n_idx;
   cudaDeviceGetAttribute(&m->n_sm, cudaDevAttrMultiProcessorCount, device);
   const size_t n_i32 = (size_t)2 * c_out + (n_groups + 1) + n_idx, off_d = (n_i32 * 4 + 15) / 16 * 16;
   std::vector<unsigned char> hbuf(off_d + (size_t)2 * c_out * 8, 0);
@@ -1233,15 +1233,16 @@ extern "C" int hga_chanmap_apply(hga_chanmap* m, const double* x_dev, int64_t T,
   if (T < 0 || ldx < m->c_in || ldo < m->c_out) return fail(HGA_ERR_INVALID, "bad shape: T=%lld ldx=%lld ldo=%lld", (long long)T, (long long)ldx, (long long)ldo);
   if (T == 0) return HGA_OK;
   CU(cudaSetDevice(m->device));
-  ChanMapArgs a{x_dev, ldx, T, m->c_in, m->c_out, m->n_groups, m->sel, m->grp, m->alpha, m->beta, m->gptr, m->gidx, out_dev, ldo};
-  const size_t smem = (size_t)kChanMapWarps * (m->c_in + kChanMapMaxGroups) * 8;
+  ChanMapArgs a{x_dev, ldx, T, m->c_in, m->c_out, m->n_groups, m->n_idx, m->sel, m->grp, m->alpha, m->beta, m->gptr, m->gidx, out_dev, ldo};
+  const size_t smem = chanmap_smem_bytes(m->c_in, m->c_out, m->n_groups, m->n_idx);
+  if (smem > 227 * 1024) return fail(HGA_ERR_UNSUPPORTED, "channel map needs %zu bytes of shared memory (c_in=%d c_out=%d)", smem, m->c_in, m->c_out);
   static size_t smem_set = 0;
   if (smem > 48 * 1024 && smem > smem_set) {
     CU(cudaFuncSetAttribute(k_chanmap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_set = smem;
   }
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(smem, 1)));
-  const int64_t need = (T + kChanMapWarps - 1) / kChanMapWarps;
+  const int64_t need = (T + kChanMapWarps * kChanMapRows - 1) / (kChanMapWarps * kChanMapRows);
   const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)m->n_sm * per_sm));
   k_chanmap<<<grid, 32 * kChanMapWarps, smem, (cudaStream_t)stream>>>(a);
   LAUNCHED();

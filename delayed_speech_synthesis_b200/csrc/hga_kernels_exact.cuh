@@ -330,7 +330,7 @@ __device__ __forceinline__ Moments chan_merge(Moments a, Moments b) {
 }
 
 constexpr int kStatsRowsPerBlock = 8;
-__global__ void __launch_bounds__(256) k_stats_partial(const double* __restrict__ f, int64_t F, int C, int64_t ld,
+__global__ void __launch_bounds__(256, 8) k_stats_partial(const double* __restrict__ f, int64_t F, int C, int64_t ld,
                                                        int64_t rows_per_block, double* __restrict__ part) {
   __shared__ Moments sm[kStatsRowsPerBlock][33];
   const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -341,7 +341,19 @@ __global__ void __launch_bounds__(256) k_stats_partial(const double* __restrict_
   if (c < C && r0 + ty < r1) {
     const double k = f[(r0 + ty) * ld + c];
     double s1 = 0.0, s2 = 0.0, cnt = 0.0;
-    for (int64_t r = r0 + ty; r < r1; r += kStatsRowsPerBlock) {
+    // four loads in flight per thread (the accumulation chain is loop-carried, so the compiler does not hoist them itself:
+    // one load in flight per warp gave 2.35 TB/s); the values are accumulated in the same order as row by row
+    int64_t r = r0 + ty;
+    constexpr int64_t S = kStatsRowsPerBlock;
+    for (; r + 3 * S < r1; r += 4 * S) {
+      const double v0 = f[r * ld + c], v1 = f[(r + S) * ld + c], v2 = f[(r + 2 * S) * ld + c], v3 = f[(r + 3 * S) * ld + c];
+      double d = v0 - k; s1 += d; s2 = fma(d, d, s2);
+      d = v1 - k; s1 += d; s2 = fma(d, d, s2);
+      d = v2 - k; s1 += d; s2 = fma(d, d, s2);
+      d = v3 - k; s1 += d; s2 = fma(d, d, s2);
+      cnt += 4.0;
+    }
+    for (; r < r1; r += S) {
       const double d = f[r * ld + c] - k;
       s1 += d;
       s2 = fma(d, d, s2);

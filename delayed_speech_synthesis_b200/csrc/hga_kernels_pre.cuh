@@ -13,9 +13,10 @@
 //   and any composition gather -> CAR -> gather (prepare_corpus.py:152-160, decode_online.py:69-82), which the host
 //   folds into one (sel, grp, group-table) triple expressed in RAW input columns.
 //
-// Bound: HBM.  Algorithmic bytes per input row: 8 * C_in read + 8 * C_out written.  One warp owns a row: the row is
-// staged in shared memory with coalesced 256 B loads, group means are lane-strided sums + a shuffle butterfly (fixed
-// order -> deterministic), outputs are written with coalesced 256 B stores.
+// Bound: HBM.  Algorithmic bytes per input row: 8 * C_in read + 8 * C_out written.  One warp owns two rows at a time:
+// the rows are staged in shared memory with coalesced 256 B loads (both rows' loads in flight together), group means are
+// lane-strided sums + a shuffle butterfly (fixed order -> deterministic) times a per-group reciprocal count, outputs are
+// written with coalesced 256 B stores.  The index / weight tables live in shared memory (read once per CTA).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -25,7 +26,7 @@ namespace hga {
 struct ChanMapArgs {
   const double* x;
   int64_t ldx, T;
-  int C_in, C_out, n_groups;
+  int C_in, C_out, n_groups, n_idx;
   const int32_t* sel;    // [C_out] raw column of the direct term (-1: none)
   const int32_t* grp;    // [C_out] group of the mean term (-1: none)
   const double* alpha;   // [C_out]
@@ -36,35 +37,84 @@ struct ChanMapArgs {
   int64_t ldo;
 };
 
-constexpr int kChanMapWarps = 8;     // rows in flight per CTA
+constexpr int kChanMapWarps = 8;     // warps per CTA
+constexpr int kChanMapRows = 2;      // rows a warp works on at a time (their loads are in flight together)
 constexpr int kChanMapMaxGroups = 32;
 
-__global__ void __launch_bounds__(32 * kChanMapWarps) k_chanmap(const __grid_constant__ ChanMapArgs a) {
-  extern __shared__ __align__(16) double smem_cm[];
+// Shared memory: the tables (read once per CTA instead of once per row), then per warp kChanMapRows x (row | group means).
+__host__ __device__ inline size_t chanmap_table_bytes(int C_out, int n_groups, int n_idx) {
+  size_t b = (size_t)C_out * (8 + 8) + (size_t)kChanMapMaxGroups * 8;                  // alpha, beta, 1 / count
+  b += ((size_t)2 * C_out + (n_groups + 1) + n_idx) * 4;                               // sel, grp, gptr, gidx
+  return (b + 15) / 16 * 16;
+}
+__host__ __device__ inline size_t chanmap_smem_bytes(int C_in, int C_out, int n_groups, int n_idx) {
+  return chanmap_table_bytes(C_out, n_groups, n_idx) + (size_t)kChanMapWarps * kChanMapRows * (C_in + kChanMapMaxGroups) * 8;
+}
+
+__global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_constant__ ChanMapArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_cm[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  double* row = smem_cm + (size_t)w * (a.C_in + kChanMapMaxGroups);
-  double* gmean = row + a.C_in;
-  for (int64_t t = (int64_t)blockIdx.x * kChanMapWarps + w; t < a.T; t += (int64_t)gridDim.x * kChanMapWarps) {
-    const double* xr = a.x + t * a.ldx;
-    for (int c = lane; c < a.C_in; c += 32) row[c] = xr[c];
+  double* s_alpha = reinterpret_cast<double*>(smem_cm);
+  double* s_beta = s_alpha + a.C_out;
+  double* s_ginv = s_beta + a.C_out;
+  int32_t* s_sel = reinterpret_cast<int32_t*>(s_ginv + kChanMapMaxGroups);
+  int32_t* s_grp = s_sel + a.C_out;
+  int32_t* s_gptr = s_grp + a.C_out;
+  int32_t* s_gidx = s_gptr + a.n_groups + 1;
+  for (int j = threadIdx.x; j < a.C_out; j += blockDim.x) {
+    s_alpha[j] = a.alpha[j]; s_beta[j] = a.beta[j]; s_sel[j] = a.sel[j]; s_grp[j] = a.grp[j];
+  }
+  for (int g = threadIdx.x; g <= a.n_groups; g += blockDim.x) s_gptr[g] = a.n_groups > 0 ? a.gptr[g] : 0;
+  for (int g = threadIdx.x; g < a.n_groups; g += blockDim.x) s_ginv[g] = 1.0 / (double)(a.gptr[g + 1] - a.gptr[g]);
+  for (int k = threadIdx.x; k < a.n_idx; k += blockDim.x) s_gidx[k] = a.gidx[k];
+  __syncthreads();
+  const int rstride = a.C_in + kChanMapMaxGroups;
+  double* rows = reinterpret_cast<double*>(smem_cm + chanmap_table_bytes(a.C_out, a.n_groups, a.n_idx)) + (size_t)w * kChanMapRows * rstride;
+  const int64_t step = (int64_t)gridDim.x * kChanMapWarps * kChanMapRows;
+  for (int64_t t0 = ((int64_t)blockIdx.x * kChanMapWarps + w) * kChanMapRows; t0 < a.T; t0 += step) {
+    const int nr = (int)min((int64_t)kChanMapRows, a.T - t0);
+#pragma unroll
+    for (int r = 0; r < kChanMapRows; ++r)
+      if (r < nr) {
+        const double* xr = a.x + (t0 + r) * a.ldx;
+        double* row = rows + r * rstride;
+        for (int c = lane; c < a.C_in; c += 32) row[c] = xr[c];
+      }
     __syncwarp();
     for (int g = 0; g < a.n_groups; ++g) {
-      const int k0 = a.gptr[g], k1 = a.gptr[g + 1];
-      double s = 0.0;
-      for (int k = k0 + lane; k < k1; k += 32) s += row[a.gidx[k]];
+      const int k0 = s_gptr[g], k1 = s_gptr[g + 1];
+      double s[kChanMapRows];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (lane == 0) gmean[g] = s / (double)(k1 - k0);
+      for (int r = 0; r < kChanMapRows; ++r) s[r] = 0.0;
+      for (int k = k0 + lane; k < k1; k += 32) {
+        const int col = s_gidx[k];
+#pragma unroll
+        for (int r = 0; r < kChanMapRows; ++r) s[r] += rows[r * rstride + col];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < kChanMapRows; ++r) s[r] += __shfl_xor_sync(0xffffffffu, s[r], o);
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < kChanMapRows; ++r) rows[r * rstride + a.C_in + g] = s[r] * s_ginv[g];
+      }
     }
     __syncwarp();
-    double* orow = a.out + t * a.ldo;
     for (int j = lane; j < a.C_out; j += 32) {
-      const int sj = a.sel[j], gj = a.grp[j];
-      double v = sj >= 0 ? a.alpha[j] * row[sj] : 0.0;
-      if (gj >= 0) v = fma(a.beta[j], gmean[gj], v);
-      orow[j] = v;
+      const int sj = s_sel[j], gj = s_grp[j];
+      const double al = s_alpha[j], be = s_beta[j];
+#pragma unroll
+      for (int r = 0; r < kChanMapRows; ++r)
+        if (r < nr) {
+          const double* row = rows + r * rstride;
+          double v = sj >= 0 ? al * row[sj] : 0.0;
+          if (gj >= 0) v = fma(be, row[a.C_in + gj], v);
+          a.out[(t0 + r) * a.ldo + j] = v;
+        }
     }
-    __syncwarp();  // the row buffer is reused by the next iteration
+    __syncwarp();  // the row buffers are reused by the next iteration
   }
 }
 
