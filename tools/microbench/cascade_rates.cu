@@ -146,6 +146,7 @@ void run(const char* name, int wps) {
     q.a1[s] = -1.4 + 0.01 * s; q.a2[s] = 0.95 - 0.01 * s; q.b1u[s] = s < 4 ? 2.0 : -1.45;
     auto pack = [](double v) { float f = (float)v; uint32_t u; memcpy(&u, &f, 4); return ((unsigned long long)u << 32) | u; };
     pc.na1p[s] = pack(-q.a1[s]); pc.na2p[s] = pack(-q.a2[s]); pc.b1p[s] = pack(q.b1u[s]);
+    pc.c1d[s] = -q.a1[s]; pc.c2d[s] = -q.a2[s]; pc.cbd[s] = q.b1u[s];   // k_hga_pipe2's own operand arrays (section form U)
   }
   int dev = 0, nsm = 0; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
   const int ntiles = 400;
