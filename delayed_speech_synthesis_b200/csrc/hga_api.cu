@@ -291,8 +291,7 @@ static PipeShape pipe_shape(bool f32 = false) {
   } else {
     if (p.S != 4 && p.S != 8) p.S = 4;
     if (p.S == 8) p.TB = 20;
-    else if (p.TB != 20 && p.TB != 40 && !((p.TB == 60 || p.TB == 70 || p.TB == 80) && !f32)) p.TB = 40;  // > 40-row tiles: float64 only
-    // (float32 mode: 60-row tiles fit with 2-deep rings but that kernel shape faults on the device; not debugged, not offered)
+    else if (p.TB != 20 && p.TB != 40 && p.TB != 60 && !((p.TB == 70 || p.TB == 80) && !f32)) p.TB = 40;  // 70 / 80-row tiles: float64 only
   }
   return p;
 }
@@ -359,8 +358,8 @@ static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs&
     if (hop == 10) {
       if (p.S == 8) return pipe2_launch_t<T, 8, 20, 10>(q, pc, a, tm, st, occ);
       if (p.TB == 20) return pipe2_launch_t<T, 4, 20, 10>(q, pc, a, tm, st, occ);
+      if (p.TB == 60) return pipe2_launch_t<T, 4, 60, 10>(q, pc, a, tm, st, occ);
       if constexpr (PipeTraits<T>::CPL == 1) {
-        if (p.TB == 60) return pipe2_launch_t<T, 4, 60, 10>(q, pc, a, tm, st, occ);
         if (p.TB == 70) return pipe2_launch_t<T, 4, 70, 10>(q, pc, a, tm, st, occ);
         if (p.TB == 80) return pipe2_launch_t<T, 4, 80, 10>(q, pc, a, tm, st, occ);
       }
@@ -370,8 +369,8 @@ static int pipe_dispatch(const Cascade& q, const PipeConst& pc, const FusedArgs&
     if (p.TB == 20) return pipe2_launch_t<T, 4, 20, 20>(q, pc, a, tm, st, occ);
     if constexpr (PipeTraits<T>::CPL == 1) {
       if (p.TB >= 80) return pipe2_launch_t<T, 4, 80, 20>(q, pc, a, tm, st, occ);
-      if (p.TB >= 60) return pipe2_launch_t<T, 4, 60, 20>(q, pc, a, tm, st, occ);
     }
+    if (p.TB >= 60) return pipe2_launch_t<T, 4, 60, 20>(q, pc, a, tm, st, occ);
     return pipe2_launch_t<T, 4, 40, 20>(q, pc, a, tm, st, occ);
   }
   if (hop == 10) {

@@ -337,7 +337,12 @@ __global__ void __launch_bounds__(32 * (S + NF + 1), 1) k_hga_pipe2(const __grid
   uint64_t* full_x = bars + SM::b_full_x;
   uint64_t* full_y = bars + SM::b_full_y;
   uint64_t* empty_y = bars + SM::b_empty_y;
-  constexpr int LEAD = S + 1;  // float32 mode: the framing warps convert x tile m + LEAD before they frame y tile m
+  // float32 mode: the framing warps convert x tile m + LEAD before they frame y tile m.  The converter of tile j waits on
+  // the (j / NBC - 1)-th completion of empty_c[j % NBC] by PARITY, which is only sound if completion j / NBC - 2 (tile
+  // j - 2 NBC consumed) is certain to have happened: at iteration m only tiles <= m - 1 are known to be through the
+  // filter warps, so LEAD <= 2 NBC - 1 (a 2-deep converted ring with LEAD = 5 let a converter run one phase ahead of
+  // its barrier at start-up, overwrite an unconsumed tile and hang the CTA).
+  constexpr int LEAD = (S + 1) < (2 * SM::NBC - 1) ? (S + 1) : (2 * SM::NBC - 1);
 
   const int cg = (a.C + CW - 1) / CW;
   const int item = blockIdx.x / cg, c0 = (blockIdx.x % cg) * CW;
