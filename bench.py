@@ -206,7 +206,7 @@ def stream_latency(fs, C, mu, sigma, device, n_push=10000, warm=500, chunk=10):
     rl = rl[200:] * 1e6
     return {"packet": f"{chunk} x {C} float64", "n": int(n_push), "p50_us": float(np.percentile(lat, 50)),
             "p99_us": float(np.percentile(lat, 99)), "max_us": float(lat.max()),
-            "path": "hga_stream_push_host: mapped pinned staging (zero-copy), 1 kernel (k_stream_push_sys) + 1 stream synchronise per packet, exact arithmetic",
+            "path": "hga_stream_push_host: mapped pinned staging (zero-copy), 1 kernel (k_stream_push_sys), completion slots polled in mapped memory, exact arithmetic",
             "wire_packet": {"packet": f"7-byte header + {C} x {chunk} float32", "n": int(n_pk), "p50_us": float(np.percentile(lp, 50)),
                             "p99_us": float(np.percentile(lp, 99)), "path": "hga_stream_push_packet (interpret_bytes fused into the kernel)"},
             "reference_p50_us": float(np.percentile(rl, 50)), "reference_p99_us": float(np.percentile(rl, 99)),

@@ -118,6 +118,10 @@ struct PinBuf {
 // memory (staged into shared memory) and writes the frames to mapped pinned host memory: one launch + one stream
 // synchronisation per packet instead of H2D copy + launch + D2H copy + synchronisation.  HGA_B200_STREAM_MAPPED=0 disables.
 constexpr int64_t kMappedRows = 64;
+static bool stream_flagged() {  // HGA_B200_STREAM_FLAG=0: always synchronise the stream instead of polling completion slots
+  static const bool on = [] { const char* e = getenv("HGA_B200_STREAM_FLAG"); return !(e && atoi(e) == 0); }();
+  return on;
+}
 static bool stream_mapped() {
   static const bool on = [] { const char* e = getenv("HGA_B200_STREAM_MAPPED"); return !(e && atoi(e) == 0); }();
   return on;
@@ -472,7 +476,9 @@ struct hga_handle {
   int plan_variant = -1;
   // host-buffer paths
   DevBuf xdev, outdev, mudev, sigdev;
-  PinBuf pin_in, pin_out;
+  PinBuf pin_in, pin_out, pin_flag;   // pin_flag: per-warp completion slots of the zero-copy packet path
+  unsigned long long push_seq = 0;
+  bool push_inflight = false;         // a host push returned on its completion slots; its kernel may still be storing state
   std::vector<double> mu_cache, sig_cache;
   bool musig_valid = false;
   cudaStream_t s_own = nullptr, s_copy = nullptr;
@@ -482,6 +488,14 @@ struct hga_handle {
   bool timed = false;
 };
 
+// Host pushes that poll completion slots return before their kernel has stored the new remainder / filter state on the
+// handle's own stream; anything that touches that state from another stream (or frees it) waits for it first.
+static void drain_push(hga_handle* h) {
+  if (h->push_inflight) {
+    cudaStreamSynchronize(h->s_own);
+    h->push_inflight = false;
+  }
+}
 static int tile_zi(hga_handle* h, cudaStream_t st) {
   const int C = h->cfg.n_channels, ns = h->q.ns;
   std::vector<double> z((size_t)ns * 2 * C);
@@ -558,11 +572,13 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
 extern "C" int hga_destroy(hga_handle* h) {
   if (!h) return HGA_OK;
   cudaSetDevice(h->cfg.device);
+  drain_push(h);
   for (DevBuf* b : {&h->state, &h->framebuf, &h->state2, &h->framebuf2, &h->work, &h->segs, &h->ybuf, &h->stats_part, &h->seg_state, &h->seg_rem, &h->zir,
                     &h->xdev, &h->outdev, &h->mudev, &h->sigdev})
     b->release();
   h->pin_in.release();
   h->pin_out.release();
+  h->pin_flag.release();
   for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -575,6 +591,7 @@ extern "C" int hga_destroy(hga_handle* h) {
 extern "C" int hga_reset(hga_handle* h, void* stream) {
   if (!h) return fail(HGA_ERR_INVALID, "null handle");
   CU(cudaSetDevice(h->cfg.device));
+  drain_push(h);
   return tile_zi(h, (cudaStream_t)stream);
 }
 extern "C" int hga_warmup(const hga_handle* h) { return h ? h->warmup : 0; }
@@ -819,8 +836,10 @@ static int bulk_push(hga_handle* h, const double* x, int64_t n, int64_t ldx, con
 
 // One packet through the latency kernels.  xf != nullptr: float32 [C][n] payload in place of x.  Small packets take
 // k_stream_push_sys (sections across lanes, frame rows and packet in shared memory), the rest k_stream_push.
-static void launch_stream(hga_handle* h, const PushGeom& g, const double* x, const float* xf, int64_t ldx, int64_t n, const double* mu,
-                          const double* sigma, double* out, int64_t ldo, float* out_f32, cudaStream_t st) {
+// Returns true when the launched kernel publishes `done_seq` in done_slots (one slot per pair of channels).
+static bool launch_stream(hga_handle* h, const PushGeom& g, const double* x, const float* xf, int64_t ldx, int64_t n, const double* mu,
+                          const double* sigma, double* out, int64_t ldo, float* out_f32, cudaStream_t st,
+                          unsigned long long* done_slots = nullptr, unsigned long long done_seq = 0) {
   const int C = h->cfg.n_channels;
   static const bool fast_on = [] { const char* e = getenv("HGA_B200_STREAM_FAST"); return !(e && atoi(e) == 0); }();
   if (fast_on && g.rows_total + n <= kStreamFastRows) {
@@ -829,11 +848,14 @@ static void launch_stream(hga_handle* h, const PushGeom& g, const double* x, con
     if (xf)
       k_stream_push_sys<1><<<grid, 32 * kSysWarps, smem, st>>>(h->q, xf, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
                                                                 g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
-                                                                h->cfg.eps, mu, sigma, out, ldo, out_f32);
+                                                                h->cfg.eps, mu, sigma, out, ldo, out_f32, done_slots, done_seq);
     else
       k_stream_push_sys<0><<<grid, 32 * kSysWarps, smem, st>>>(h->q, x, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
                                                                 g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
-                                                                h->cfg.eps, mu, sigma, out, ldo, out_f32);
+                                                                h->cfg.eps, mu, sigma, out, ldo, out_f32, done_slots, done_seq);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    h->first_frame = 0;
+    return done_slots != nullptr;
   } else {
     k_stream_push<<<(C + 31) / 32, 32, 0, st>>>(h->q, x, ldx, (int)n, C, h->state.as<double>(), h->framebuf.as<double>(), g.y_row0,
                                                 g.zero_rows, g.rows_total, h->overlap, (int)g.frames, h->cfg.frame_len, h->cfg.hop,
@@ -841,6 +863,25 @@ static void launch_stream(hga_handle* h, const PushGeom& g, const double* x, con
   }
   g_launches.fetch_add(1, std::memory_order_relaxed);
   h->first_frame = 0;
+  return false;
+}
+// Wait until the frames of the push that published `seq` are in host memory: poll the per-warp slots (mapped pinned
+// memory) for a bounded time, then fall back to synchronising the stream (also the path that surfaces a kernel fault).
+static int wait_frames(hga_handle* h, bool flagged, unsigned long long seq, int n_slots, cudaStream_t st) {
+  if (flagged) {
+    const volatile unsigned long long* slots = h->pin_flag.as<const volatile unsigned long long>();
+    for (int spin = 0; spin < 200000; ++spin) {
+      int k = 0;
+      while (k < n_slots && slots[k] == seq) ++k;
+      if (k == n_slots) { std::atomic_thread_fence(std::memory_order_acquire); h->push_inflight = true; return HGA_OK; }
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    }
+  }
+  CU(cudaStreamSynchronize(st));
+  h->push_inflight = false;
+  return HGA_OK;
 }
 static int stream_push_dev(hga_handle* h, const double* x, int64_t n, int64_t ldx, const double* mu, const double* sigma,
                            double* out, int64_t ldo, int64_t* n_frames, cudaStream_t st) {
@@ -861,6 +902,7 @@ extern "C" int hga_stream_push(hga_handle* h, const double* x_dev, int64_t n, in
   if (!h || !x_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
   if (ldx < h->cfg.n_channels || ldo < h->cfg.n_channels) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
   CU(cudaSetDevice(h->cfg.device));
+  drain_push(h);
   return stream_push_dev(h, x_dev, n, ldx, mu_dev, sigma_dev, out_dev, ldo, n_frames, (cudaStream_t)stream);
 }
 
@@ -913,6 +955,10 @@ extern "C" int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t
   if ((rc = h->pin_in.reserve(in_bytes)) || (rc = h->pin_out.reserve(out_bytes)) || (rc = h->xdev.reserve(in_bytes)) ||
       (rc = h->outdev.reserve(out_bytes)))
     return rc;
+  if (!h->pin_flag.p) {
+    if ((rc = h->pin_flag.reserve((size_t)((C + 1) / 2) * 8))) return rc;
+    memset(h->pin_flag.p, 0, (size_t)((C + 1) / 2) * 8);
+  }
   const double *mu_d, *sig_d;
   if ((rc = sync_musigma(h, mu_host, sigma_host, st, &mu_d, &sig_d))) return rc;
   // gather rows into pinned staging (compacts ldx -> C), one H2D, one kernel, one D2H
@@ -920,10 +966,12 @@ extern "C" int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t
   if (ldx == C) memcpy(pin, x_host, in_bytes);
   else for (int64_t r = 0; r < n; ++r) memcpy(pin + r * C, x_host + r * ldx, (size_t)C * 8);
   int64_t nf = 0;
+  bool flagged = false;
   double* in_map = h->pin_in.dev<double>();
   double* out_map = h->pin_out.dev<double>();
   if (stream_mapped() && n <= kMappedRows && in_map && out_map) {  // zero-copy: see kMappedRows
-    launch_stream(h, g, in_map, nullptr, C, n, mu_d, sig_d, out_map, C, nullptr, st);
+    unsigned long long* slots = stream_flagged() ? h->pin_flag.dev<unsigned long long>() : nullptr;
+    flagged = launch_stream(h, g, in_map, nullptr, C, n, mu_d, sig_d, out_map, C, nullptr, st, slots, ++h->push_seq);
     CU(cudaGetLastError());
     nf = g.frames;
   } else {
@@ -931,7 +979,7 @@ extern "C" int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t
     if ((rc = stream_push_dev(h, h->xdev.as<double>(), n, C, mu_d, sig_d, h->outdev.as<double>(), C, &nf, st))) return rc;
     if (nf > 0) CU(cudaMemcpyAsync(h->pin_out.p, h->outdev.p, (size_t)nf * C * 8, cudaMemcpyDeviceToHost, st));
   }
-  CU(cudaStreamSynchronize(st));
+  if ((rc = wait_frames(h, flagged, h->push_seq, (C + 1) / 2, st))) return rc;
   const double* po = h->pin_out.as<double>();
   if (ldo == C) memcpy(out_host, po, (size_t)nf * C * 8);
   else for (int64_t r = 0; r < nf; ++r) memcpy(out_host + r * ldo, po + r * C, (size_t)C * 8);
@@ -1000,14 +1048,20 @@ extern "C" int hga_stream_push_packet(hga_handle* h, const void* packet_host, in
   if ((rc = h->pin_in.reserve(in_bytes)) || (rc = h->pin_out.reserve(out_bytes)) || (rc = h->xdev.reserve(in_bytes)) ||
       (rc = h->outdev.reserve(out_bytes)))
     return rc;
+  if (!h->pin_flag.p) {
+    if ((rc = h->pin_flag.reserve((size_t)((C + 1) / 2) * 8))) return rc;
+    memset(h->pin_flag.p, 0, (size_t)((C + 1) / 2) * 8);
+  }
   const double *mu_d, *sig_d;
   if ((rc = sync_musigma(h, mu_host, sigma_host, st, &mu_d, &sig_d))) return rc;
   memcpy(h->pin_in.p, payload, in_bytes);
   const int64_t nf = g.frames;
+  bool flagged = false;
   float* in_map = h->pin_in.dev<float>();
   double* out_map = h->pin_out.dev<double>();
   if (stream_mapped() && n <= kMappedRows && in_map && out_map) {
-    launch_stream(h, g, nullptr, in_map, C, n, mu_d, sig_d, out_map, C, out_f32_dev, st);
+    unsigned long long* slots = stream_flagged() ? h->pin_flag.dev<unsigned long long>() : nullptr;
+    flagged = launch_stream(h, g, nullptr, in_map, C, n, mu_d, sig_d, out_map, C, out_f32_dev, st, slots, ++h->push_seq);
     CU(cudaGetLastError());
   } else {
     CU(cudaMemcpyAsync(h->xdev.p, h->pin_in.p, in_bytes, cudaMemcpyHostToDevice, st));
@@ -1016,7 +1070,7 @@ extern "C" int hga_stream_push_packet(hga_handle* h, const void* packet_host, in
     if (nf > 0) CU(cudaMemcpyAsync(h->pin_out.p, h->outdev.p, (size_t)nf * C * 8, cudaMemcpyDeviceToHost, st));
   }
   h->first_frame = 0;
-  CU(cudaStreamSynchronize(st));
+  if ((rc = wait_frames(h, flagged, h->push_seq, (C + 1) / 2, st))) return rc;
   const double* po = h->pin_out.as<double>();
   if (ldo == C) memcpy(out_host, po, (size_t)nf * C * 8);
   else for (int64_t r = 0; r < nf; ++r) memcpy(out_host + r * ldo, po + r * C, (size_t)C * 8);

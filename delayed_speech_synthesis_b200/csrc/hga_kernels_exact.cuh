@@ -218,7 +218,12 @@ __global__ void __launch_bounds__(32 * kSysWarps) k_stream_push_sys(const __grid
                                                                     int y_row0, int zero_rows, int rows_total, int overlap, int n_frames,
                                                                     int L, int hop, double eps, const double* __restrict__ mu,
                                                                     const double* __restrict__ sigma, double* __restrict__ out,
-                                                                    int64_t ldo, float* __restrict__ out_f32) {
+                                                                    int64_t ldo, float* __restrict__ out_f32,
+                                                                    unsigned long long* __restrict__ done_slots = nullptr,
+                                                                    unsigned long long done_seq = 0) {
+  // done_slots != nullptr (mapped host memory, one slot per warp): once a warp's frames are stored, it publishes
+  // done_seq in its slot; the host polls the slots instead of synchronising the stream (the frames are all it needs:
+  // remainder and state are device-side and the next push is stream-ordered behind this kernel).
   extern __shared__ __align__(16) double ssm[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int s = lane & 15, chl = lane >> 4;
@@ -279,6 +284,14 @@ __global__ void __launch_bounds__(32 * kSysWarps) k_stream_push_sys(const __grid
       const double f = feature(acc, (double)L, eps, zs, m, sd);
       out[(int64_t)w * ldo + c] = f;
       if (out_f32 != nullptr) out_f32[(int64_t)w * C + c] = (float)f;
+    }
+  }
+  if (done_slots != nullptr) {
+    __threadfence_system();   // every lane: its frame stores are visible system-wide before the slot is
+    __syncwarp();
+    if (lane == 0) {
+      *reinterpret_cast<volatile unsigned long long*>(done_slots + (cbase >> 1)) = done_seq;
+      __threadfence_system();
     }
   }
   // ---- burst 3: new remainder (the last `overlap` rows) and filter state
