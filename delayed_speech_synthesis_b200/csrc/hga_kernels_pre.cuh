@@ -39,7 +39,7 @@ struct ChanMapArgs {
 
 constexpr int kChanMapWarps = 8;     // warps per CTA
 constexpr int kChanMapRows = 2;      // rows a warp works on at a time (their loads are in flight together)
-constexpr int kChanMapMaxGroups = 32;
+constexpr int kChanMapMaxGroups = 64;
 
 // Shared memory: the tables (read once per CTA instead of once per row), then per warp kChanMapRows x (row | group means).
 __host__ __device__ inline size_t chanmap_table_bytes(int C_out, int n_groups, int n_idx) {

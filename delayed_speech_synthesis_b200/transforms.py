@@ -29,6 +29,9 @@ from . import _lib
 from ._lib import check
 
 
+MAX_GROUPS = 64   # kChanMapMaxGroups (csrc/hga_kernels_pre.cuh)
+
+
 @dataclass
 class ChannelMapSpec:
     c_in: int
@@ -126,6 +129,8 @@ def fold(transforms: Optional[Sequence[Callable]], c_in: int) -> Optional[Channe
             if spec is None:
                 return None
     except (IndexError, ValueError, TypeError):
+        return None
+    if len(spec.groups) > MAX_GROUPS:      # more averaging groups than the kernel's table holds: the callables run as they are
         return None
     return spec
 

@@ -181,7 +181,7 @@ int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t C, double*
  *   - BadChannelCorrection.__call__ (local/common.py:279-284): alpha 0, beta 1, group = the bad channel's neighbours;
  *   - and gather -> CAR -> gather chains (prepare_corpus.py:152-160, decode_online.py:69-82) folded by the host into
  *     raw-column indices.  sel[j] = -1 / grp[j] = -1 drop the respective term.  Groups are CSR: columns
- *     gidx[gptr[g] .. gptr[g+1]) (raw input columns), at most 32 groups.  All table arguments are HOST arrays, copied
+ *     gidx[gptr[g] .. gptr[g+1]) (raw input columns), at most 64 groups.  All table arguments are HOST arrays, copied
  *     at creation.  In place (out == x, ldo == ldx) is allowed. */
 typedef struct hga_chanmap hga_chanmap;
 int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, const int32_t* sel, const int32_t* grp,

@@ -91,6 +91,8 @@ def test_fold_refuses_what_one_map_cannot_express():
     assert TR.fold([lambda d: d * 2.0], 128) is None                   # unknown callable
     assert TR.fold([both], 64) is None                                 # index out of range for the input width
     assert TR.fold(None, 128) is None and TR.fold([], 128) is None
+    many_bad = TR.BadChannelCorrection(list(range(1, 128, 2)) + [2, 4], _grids(), G["layout"])   # 66 patches > 64 groups
+    assert len(many_bad) == 66 and TR.fold([many_bad], 128) is None
 
 
 def test_fold_recognises_reference_objects_by_attribute():
@@ -183,3 +185,12 @@ def test_extractor_with_reference_transform_chain():
     for t in range(0, 200, 10):
         a, b = ex2.extract_features(x[t:t + 10]), ref2.extract_features(x[t:t + 10])
         assert a.shape == b.shape and np.abs(a - b).max() <= 1e-11
+
+
+@pytest.mark.gpu
+def test_bad_channel_correction_many_patches():
+    """Every second channel bad (64 patches = the kernel's group table full): all group means reduced in four passes."""
+    bad = list(range(1, 128, 2))
+    bcc = TR.BadChannelCorrection(bad, _grids(), G["layout"])
+    want = O.bad_channel_correction(G["f"], O.bad_channel_patches(bad, _grids(), G["layout"]))
+    assert np.abs(bcc(G["f"]) - want).max() <= TOL
