@@ -48,7 +48,7 @@ __host__ __device__ inline size_t chanmap_table_bytes(int C_out, int n_groups, i
   return (b + 15) / 16 * 16;
 }
 __host__ __device__ inline size_t chanmap_smem_bytes(int C_in, int C_out, int n_groups, int n_idx) {
-  return chanmap_table_bytes(C_out, n_groups, n_idx) + (size_t)kChanMapWarps * kChanMapRows * (C_in + kChanMapMaxGroups) * 8;
+  return chanmap_table_bytes(C_out, n_groups, n_idx) + (size_t)kChanMapWarps * kChanMapRows * (C_in + n_groups) * 8;
 }
 
 __global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_constant__ ChanMapArgs a) {
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_
   for (int g = threadIdx.x; g < a.n_groups; g += blockDim.x) s_ginv[g] = 1.0 / (double)(a.gptr[g + 1] - a.gptr[g]);
   for (int k = threadIdx.x; k < a.n_idx; k += blockDim.x) s_gidx[k] = a.gidx[k];
   __syncthreads();
-  const int rstride = a.C_in + kChanMapMaxGroups;
+  const int rstride = a.C_in + a.n_groups;   // a row of x followed by its group means
   double* rows = reinterpret_cast<double*>(smem_cm + chanmap_table_bytes(a.C_out, a.n_groups, a.n_idx)) + (size_t)w * kChanMapRows * rstride;
   const int64_t step = (int64_t)gridDim.x * kChanMapWarps * kChanMapRows;
   for (int64_t t0 = ((int64_t)blockIdx.x * kChanMapWarps + w) * kChanMapRows; t0 < a.T; t0 += step) {
