@@ -759,7 +759,7 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
   LAUNCHED();
   if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; }
   if (n_seg > 65535) return fail(HGA_ERR_UNSUPPORTED, "more than 65535 segments per call");
-  dim3 g2((unsigned)cg, (unsigned)((maxF + 7) / 8), (unsigned)n_seg);
+  dim3 g2((unsigned)cg, (unsigned)((maxF + kFramesPerBlock - 1) / kFramesPerBlock), (unsigned)n_seg);
   k_frames_seq<<<g2, 256, 0, st>>>(y, C, 0, h->segs.as<Segment>(), Segment{}, n_seg, C, maxF, L, hop, nullptr, nullptr, h->cfg.eps, mu, sigma, out, ldo);
   LAUNCHED();
   if (rem_out) {
@@ -1143,7 +1143,7 @@ extern "C" int hga_log_power(int32_t device, const double* data_dev, int64_t row
   const int64_t per = 65535LL * 8;
   for (int64_t w0 = 0; w0 < n_frames; w0 += per) {
     const int64_t nf = std::min(per, n_frames - w0);
-    dim3 gg(g.x, (unsigned)((nf + 7) / 8), 1);
+    dim3 gg(g.x, (unsigned)((nf + kFramesPerBlock - 1) / kFramesPerBlock), 1);
     // window w0+w: shift the data origin for regular windows, the index arrays for irregular ones
     if (!start_dev) {
       const int64_t shift = w0 * hop;  // logical rows to skip
@@ -1166,8 +1166,11 @@ extern "C" int hga_zscore(int32_t device, const double* f_dev, int64_t F, int32_
   if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
   CU(cudaSetDevice(device));
   if (F == 0) return HGA_OK;
-  const int64_t n = F * C;
-  k_zscore<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(f_dev, F, C, ld, mu_dev, sigma_dev, out_dev, ldo);
+  int n_sm = 148;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+  const unsigned cgz = (unsigned)((C + 31) / 32);
+  const unsigned gy = (unsigned)std::max<int64_t>(1, std::min<int64_t>((F + 31) / 32, (int64_t)n_sm * 8 / cgz + 1));
+  k_zscore<<<dim3(cgz, gy), 256, 0, (cudaStream_t)stream>>>(f_dev, F, C, ld, mu_dev, sigma_dev, out_dev, ldo);
   LAUNCHED();
   return HGA_OK;
 }

@@ -10,6 +10,8 @@ from __future__ import annotations
 from functools import lru_cache
 from typing import Tuple
 
+import functools
+
 import numpy as np
 from scipy.signal import iirfilter, sosfilt_zi
 
@@ -63,7 +65,21 @@ def window_geometry(fs: int, window_length: float, window_shift: float) -> Tuple
 
 def window_indices(rows: int, sr: int, window_length: float, window_shift: float) -> Tuple[np.ndarray, np.ndarray]:
     """(start, stop) of every window exactly as compute_log_power_features derives them (hga_optimized.pyx:36,43-44):
-    float32 products, libm floor/round on the promoted double."""
+    float32 products, libm floor/round on the promoted double.  Cached per geometry: an hour of data is 360 k windows
+    (tens of milliseconds of numpy), and callers repeat geometries (fixed packet sizes, equal trial lengths)."""
+    start, stop = _window_indices_cached(int(rows), int(sr), float(window_length), float(window_shift))
+    return start, stop
+
+
+@functools.lru_cache(maxsize=32)
+def _window_indices_cached(rows: int, sr: int, window_length: float, window_shift: float):
+    start, stop = _window_indices(rows, sr, window_length, window_shift)
+    start.setflags(write=False)
+    stop.setflags(write=False)
+    return start, stop
+
+
+def _window_indices(rows: int, sr: int, window_length: float, window_shift: float) -> Tuple[np.ndarray, np.ndarray]:
     f32 = np.float32
     wl, ws, srf = f32(window_length), f32(window_shift), f32(sr)
     num = int(np.floor(np.float64((f32(rows) - wl * srf) / (ws * srf)))) + 1
@@ -86,3 +102,10 @@ def windows_are_regular(start: np.ndarray, stop: np.ndarray, L: int, hop: int, r
         return True
     w = np.arange(n, dtype=np.int64)
     return bool(np.array_equal(start, w * hop) and np.array_equal(stop, start + L) and stop[-1] <= rows)
+
+
+@functools.lru_cache(maxsize=32)
+def window_plan(rows: int, sr: int, window_length: float, window_shift: float, L: int, hop: int):
+    """(start, stop, regular) for a geometry, cached: `window_indices` plus `windows_are_regular`."""
+    start, stop = window_indices(rows, sr, window_length, window_shift)
+    return start, stop, windows_are_regular(start, stop, L, hop, rows)

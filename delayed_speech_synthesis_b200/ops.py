@@ -62,18 +62,17 @@ def log_power(data, sr: int, window_length: float, window_shift: float, mu=None,
         d = d.contiguous()
     rows, Cn = d.shape
     L, hop = filters.window_geometry(sr, window_length, window_shift)
-    start, stop = filters.window_indices(rows + zero_rows, sr, window_length, window_shift)
+    start, stop, regular = filters.window_plan(int(rows + zero_rows), int(sr), float(window_length), float(window_shift), int(L), int(hop))
     F = len(start)
     dev = _dev_index(d)
     out = torch.empty((F, Cn), dtype=torch.float64, device=d.device)
     if F == 0:
         return out.cpu().numpy() if as_numpy else out
-    regular = filters.windows_are_regular(start, stop, L, hop, rows + zero_rows)
     sd = ed = None
     if not regular:
         if F and (start.min() < 0 or stop.max() > rows + zero_rows):
             raise ValueError("window indices fall outside the data (the reference would read out of bounds)")
-        sd, ed = torch.from_numpy(start).to(d.device), torch.from_numpy(stop).to(d.device)
+        sd, ed = torch.from_numpy(start.copy()).to(d.device), torch.from_numpy(stop.copy()).to(d.device)
     mu_t = sg_t = None
     if mu is not None:
         mu_t = torch.as_tensor(mu, dtype=torch.float64, device=d.device).reshape(-1).expand(Cn).contiguous()

@@ -49,4 +49,13 @@ f = torch.randn((360_000 * 8, C), dtype=torch.float64, device="cuda")   # featur
 st = ChannelStats(C, 0)
 s = timed(lambda: ChannelStats(C, 0).update(f))
 out["baseline stats (n, mean, M2) of 2.88 M x 128 features"] = {"ms": s * 1e3, "GB/s": f.numel() * 8 / s / 1e9, "frac_hbm": f.numel() * 8 / s / 1e9 / peak}
+from delayed_speech_synthesis_b200 import ops
+mu_t, sg_t = torch.zeros(C, dtype=torch.float64, device="cuda"), torch.ones(C, dtype=torch.float64, device="cuda")
+s = timed(lambda: ops.log_power(x, 1000, 0.05, 0.01), n=5, warm=2)      # includes the host-side window-index arithmetic of the call
+F = (T - 50) // 10 + 1
+gb = (T * C * 8 + F * C * 8) / s / 1e9
+out["compute_log_power_features (k_frames_seq, exact row-order sums) 3.6 M x 128"] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}
+s = timed(lambda: ops.zscore(f, mu_t, sg_t))
+gb = 2 * f.numel() * 8 / s / 1e9
+out["zscore 2.88 M x 128"] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}
 print(json.dumps({"peak_hbm_gbs": peak, "kernels": out}, indent=1))
