@@ -328,7 +328,32 @@ def run_b200(args):
         e2e_ok = bool(torch.equal(oh.to(dev), out))
         e2e = {"value": world * C * T / dt, "unit": UNIT, "h2d_bytes_per_step": int(T * C * 8), "d2h_bytes_per_step": int(F * C * 8),
                "ms_per_step": 1e3 * dt, "matches_device_result": e2e_ok}
-        del xh, oh
+        del xh
+        # side line: the same call fed with int16 amplifier counts + per-channel gain (BCI2000MatFile.signals() formed on
+        # the device, hga_extract_offline_raw_host): a quarter of the upload bytes.  Not the headline: the input differs.
+        if world == 1:
+            try:
+                from delayed_speech_synthesis_b200 import transforms as TR
+                gain_h = np.linspace(0.05, 0.15, C)
+                counts = torch.clamp(torch.round(x / torch.from_numpy(gain_h).to(dev)), -32000, 32000).to(torch.int16)
+                ch = torch.empty((T, C), dtype=torch.int16, pin_memory=True)
+                ch.copy_(counts)
+                ident = TR.ChannelMap(TR.ChannelMapSpec.identity(C), eng.device)
+                cn = ch.numpy()
+                eng.extract_offline_raw(cn, ident, gain_h, None, mu_h, sg_h, out=on)
+                t0 = time.perf_counter()
+                for _ in range(n_e2e):
+                    eng.extract_offline_raw(cn, ident, gain_h, None, mu_h, sg_h, out=on)
+                torch.cuda.synchronize()
+                dtr = (time.perf_counter() - t0) / n_e2e
+                want = eng.extract_offline(ident.apply_raw(counts, gain_h), None, mu, sigma)
+                e2e["raw_int16"] = {"value": C * T / dtr, "unit": UNIT, "ms_per_step": 1e3 * dtr, "h2d_bytes_per_step": int(T * C * 2),
+                                    "d2h_bytes_per_step": int(F * C * 8), "matches_device_result": bool(torch.equal(oh.to(dev), want)),
+                                    "path": "hga_extract_offline_raw_host: int16 counts x float64 gain expanded on the device (k_chanmap<int16, gain>)"}
+                del ch, counts, want
+            except Exception as exc:
+                e2e["raw_int16"] = {"error": repr(exc)}
+        del oh
     except Exception as exc:  # report, do not hide
         e2e = {"value": None, "unit": UNIT, "error": repr(exc)}
 

@@ -49,7 +49,7 @@ def trial_segments(trial_indices, fs: float, n_rows: int, tail: float = 0.04):
 
 def extract_trials(ecog, trial_indices, fs: int, nb_electrodes: int, pre_transforms=None, post_transforms=None,
                    window_length: float = 0.05, window_shift: float = 0.01, l_freq: float = 70, h_freq: float = 170,
-                   tail: float = 0.04, precision: str = "f64", device: Optional[int] = None):
+                   tail: float = 0.04, precision: str = "f64", device: Optional[int] = None, gain=None):
     """`FeatureExtractionPipeline.get_features` (prepare_corpus.py:42-52) as ONE batched launch (the part
     that needs no file I/O): every trial is filtered by a fresh extractor (initial state sosfilt_zi, fresh frame buffer),
     the features of all trials are concatenated.  The reference builds a `HighGammaExtractor` per trial and loops in Python.
@@ -57,6 +57,10 @@ def extract_trials(ecog, trial_indices, fs: int, nb_electrodes: int, pre_transfo
     ecog: (T, C_in) float64 ndarray, e.g. `BCI2000MatFile.signals()`.  pre/post transforms as for `HighGammaExtractor`:
     chains of the reference's selection / CAR / bad-channel objects run as one channel-map kernel over the whole recording
     (they are row-wise, so slicing before or after is the same); anything else is called per trial like the reference does.
+    gain: when given, `ecog` is the file's raw `signal` matrix (int16 / int32 / float32 / float64 counts) and `gain` its
+    `SourceChGain` vector (`BCI2000MatFile.raw()`): the product `signal * gain` of `BCI2000MatFile.signals()`
+    (local/common.py:456-459) is formed on the device in the load stage of the channel-map kernel, so the upload is the raw
+    element size (2 or 4 B per channel-sample instead of 8).
     Returns a (sum of frames, nb_electrodes) float64 ndarray."""
     import numpy as np
     import torch
@@ -67,7 +71,12 @@ def extract_trials(ecog, trial_indices, fs: int, nb_electrodes: int, pre_transfo
     ecog = np.asarray(ecog)
     if ecog.ndim != 2:
         raise ValueError(f"expected (T, C) data, got {ecog.shape}")
-    if ecog.dtype != np.float64:
+    if gain is not None:
+        ecog = _raw_supported(ecog)
+        gain = np.asarray(gain, dtype=np.float64)
+        if gain.ndim > 1 or (gain.ndim == 1 and len(gain) not in (1, ecog.shape[1])):
+            raise ValueError(f"gain of shape {gain.shape} does not broadcast over {ecog.shape[1]} channels")
+    elif ecog.dtype != np.float64:
         ecog = ecog.astype(np.float64)
     eng = HgaEngine(fs, nb_electrodes, window_length, window_shift, l_freq, h_freq, precision=precision, device=device)
     dev = eng.device
@@ -77,13 +86,20 @@ def extract_trials(ecog, trial_indices, fs: int, nb_electrodes: int, pre_transfo
     if pre_transforms and (spec is None or spec.c_out != nb_electrodes):
         # unfoldable chain: the user's callables see each trial slice, exactly as the reference calls them; the results are
         # laid end to end and become the segment table of the one launch
-        parts = [np.asarray(_compose(pre_transforms)(ecog[a:b])) for a, b in segs]
+        scaled = (lambda v: v) if gain is None else (lambda v: v * gain)   # what signals() hands the user's callables
+        parts = [np.asarray(_compose(pre_transforms)(scaled(ecog[a:b]))) for a, b in segs]
         offs = np.concatenate([[0], np.cumsum([len(p) for p in parts])])
         x = torch.from_numpy(np.ascontiguousarray(np.concatenate(parts) if parts else np.zeros((0, nb_electrodes)), dtype=np.float64)).cuda(dev)
         segs = [(int(offs[i]), int(offs[i + 1])) for i in range(len(parts))]
     else:
+        if gain is not None and not post_transforms and segs and all(b - a >= L for a, b in segs):
+            # every trial fills a window: upload slabs of raw counts, expand and extract on the device, all inside one call
+            cmap = transforms.ChannelMap(spec or transforms.ChannelMapSpec.identity(ecog.shape[1]), dev)
+            return eng.extract_offline_raw(ecog, cmap, gain, segs)
         x = torch.from_numpy(np.ascontiguousarray(ecog)).cuda(dev)
-        if spec is not None:
+        if gain is not None:
+            x = transforms.ChannelMap(spec or transforms.ChannelMapSpec.identity(ecog.shape[1]), dev).apply_raw(x, gain)
+        elif spec is not None:
             x = transforms.ChannelMap(spec, dev).apply(x)
     if x.shape[1] != nb_electrodes:
         raise ValueError(f"expected {nb_electrodes} channels after the pre-transforms, got {x.shape[1]}")
@@ -110,6 +126,63 @@ def extract_trials(ecog, trial_indices, fs: int, nb_electrodes: int, pre_transfo
             # the reference applies post-transforms per trial; row-wise callables commute with the concatenation
             return np.concatenate([np.asarray(_compose(post_transforms)(f.cpu().numpy())) for f in feats]) if feats else res.cpu().numpy()
     return res.cpu().numpy()
+
+
+def _raw_supported(a):
+    """Element types the raw-ingest kernel reads (float64, float32, int32, int16); narrower or unsigned integers are widened
+    losslessly on the host, 64-bit integers go to float64 as numpy's own promotion with a float64 gain would."""
+    import numpy as np
+
+    if a.dtype in (np.float64, np.float32, np.int32, np.int16):
+        return a
+    if a.dtype in (np.int8, np.uint8):
+        return a.astype(np.int16)
+    if a.dtype == np.uint16:
+        return a.astype(np.int32)
+    if a.dtype.kind in "iub" or a.dtype == np.float16:
+        return a.astype(np.float64)
+    raise TypeError(f"raw signal of dtype {a.dtype} is not real-valued")
+
+
+class BCI2000MatFile:
+    """The accessors of the reference's `.mat` wrapper that feed this path (local/common.py:399-470): sampling rate, channel
+    bookkeeping and the signal matrix.  `raw()` returns the two factors of `signals()` so that `extract_trials(..., gain=)`
+    can form the product on the device.  Trial / stimulus index extraction (the per-experiment `StimulusCode` state machines,
+    local/common.py:676-881) stays with the reference: its (label, start, stop) list is what `extract_trials` takes."""
+
+    def __init__(self, mat_filename: str):
+        from scipy.io import loadmat
+
+        self.mat_filename = mat_filename
+        self.mat = loadmat(self.mat_filename, simplify_cells=True)
+        self.fs = self.mat['parameters']['SamplingRate']['NumericValue']
+
+    def bad_channels(self):
+        if 'bad_channels' not in self.mat:
+            return None
+        bad = self.mat['bad_channels']
+        if hasattr(bad, "tolist"):
+            bad = bad.tolist()
+        bad = bad if isinstance(bad, list) else [bad]
+        return [int(name[4:]) for name in bad]          # 'chan17' -> 17
+
+    def contaminated_channels(self):
+        if 'contaminated_electrodes' not in self.mat:
+            return None
+        c = self.mat['contaminated_electrodes']
+        return [c] if isinstance(c, int) else c.tolist()
+
+    def raw(self):
+        return self.mat['signal'], self.mat['parameters']['SourceChGain']['NumericValue']
+
+    def signals(self):
+        signal, gain = self.raw()
+        return signal * gain
+
+    def ordered_stimulus_codes(self):
+        import numpy as np
+
+        return sorted(np.unique(self.mat['states']['StimulusCode']).tolist())[1:]
 
 
 def _compose(functions):

@@ -475,7 +475,7 @@ struct hga_handle {
   std::vector<int64_t> plan_key;  // seg_start/len/out_row of the cached plan
   int plan_variant = -1;
   // host-buffer paths
-  DevBuf xdev, outdev, mudev, sigdev;
+  DevBuf xdev, outdev, mudev, sigdev, rawdev;
   PinBuf pin_in, pin_out, pin_flag;   // pin_flag: per-warp completion slots of the zero-copy packet path
   unsigned long long push_seq = 0;
   bool push_inflight = false;         // a host push returned on its completion slots; its kernel may still be storing state
@@ -574,7 +574,7 @@ extern "C" int hga_destroy(hga_handle* h) {
   cudaSetDevice(h->cfg.device);
   drain_push(h);
   for (DevBuf* b : {&h->state, &h->framebuf, &h->state2, &h->framebuf2, &h->work, &h->segs, &h->ybuf, &h->stats_part, &h->seg_state, &h->seg_rem, &h->zir,
-                    &h->xdev, &h->outdev, &h->mudev, &h->sigdev})
+                    &h->xdev, &h->outdev, &h->mudev, &h->sigdev, &h->rawdev})
     b->release();
   h->pin_in.release();
   h->pin_out.release();
@@ -1284,25 +1284,45 @@ extern "C" int hga_chanmap_destroy(hga_chanmap* m) {
   delete m;
   return HGA_OK;
 }
-extern "C" int hga_chanmap_apply(hga_chanmap* m, const double* x_dev, int64_t T, int64_t ldx, double* out_dev, int64_t ldo, void* stream) {
-  if (!m || !x_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
-  if (T < 0 || ldx < m->c_in || ldo < m->c_out) return fail(HGA_ERR_INVALID, "bad shape: T=%lld ldx=%lld ldo=%lld", (long long)T, (long long)ldx, (long long)ldo);
-  if (T == 0) return HGA_OK;
-  CU(cudaSetDevice(m->device));
-  ChanMapArgs a{x_dev, ldx, T, m->c_in, m->c_out, m->n_groups, m->n_idx, m->sel, m->grp, m->alpha, m->beta, m->gptr, m->gidx, out_dev, ldo};
-  const size_t smem = chanmap_smem_bytes(m->c_in, m->c_out, m->n_groups, m->n_idx);
-  if (smem > 227 * 1024) return fail(HGA_ERR_UNSUPPORTED, "channel map needs %zu bytes of shared memory (c_in=%d c_out=%d)", smem, m->c_in, m->c_out);
-  static size_t smem_set = 0;
+template <typename IN, bool GAIN>
+static int chanmap_launch(hga_chanmap* m, const ChanMapArgs& a, size_t smem, cudaStream_t stream) {
+  static size_t smem_set = 0;  // per instantiation
   if (smem > 48 * 1024 && smem > smem_set) {
-    CU(cudaFuncSetAttribute(k_chanmap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaFuncSetAttribute(k_chanmap<IN, GAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_set = smem;
   }
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(smem, 1)));
-  const int64_t need = (T + kChanMapWarps * kChanMapRows - 1) / (kChanMapWarps * kChanMapRows);
+  const int64_t need = (a.T + kChanMapWarps * kChanMapRows - 1) / (kChanMapWarps * kChanMapRows);
   const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)m->n_sm * per_sm));
-  k_chanmap<<<grid, 32 * kChanMapWarps, smem, (cudaStream_t)stream>>>(a);
+  k_chanmap<IN, GAIN><<<grid, 32 * kChanMapWarps, smem, stream>>>(a);
   LAUNCHED();
   return HGA_OK;
+}
+template <typename IN>
+static int chanmap_launch_g(hga_chanmap* m, const ChanMapArgs& a, size_t smem, cudaStream_t stream) {
+  return a.gain ? chanmap_launch<IN, true>(m, a, smem, stream) : chanmap_launch<IN, false>(m, a, smem, stream);
+}
+
+extern "C" int hga_chanmap_apply_raw(hga_chanmap* m, const void* x_dev, int32_t dtype, const double* gain_dev, int64_t T, int64_t ldx,
+                                     double* out_dev, int64_t ldo, void* stream) {
+  if (!m || !x_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (T < 0 || ldx < m->c_in || ldo < m->c_out) return fail(HGA_ERR_INVALID, "bad shape: T=%lld ldx=%lld ldo=%lld", (long long)T, (long long)ldx, (long long)ldo);
+  if (dtype < HGA_RAW_F64 || dtype > HGA_RAW_I16) return fail(HGA_ERR_INVALID, "unknown raw dtype %d", dtype);
+  if (T == 0) return HGA_OK;
+  CU(cudaSetDevice(m->device));
+  ChanMapArgs a{x_dev, gain_dev, ldx, T, m->c_in, m->c_out, m->n_groups, m->n_idx, m->sel, m->grp, m->alpha, m->beta, m->gptr, m->gidx, out_dev, ldo};
+  const size_t smem = chanmap_smem_bytes(m->c_in, m->c_out, m->n_groups, m->n_idx);
+  if (smem > 227 * 1024) return fail(HGA_ERR_UNSUPPORTED, "channel map needs %zu bytes of shared memory (c_in=%d c_out=%d)", smem, m->c_in, m->c_out);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (dtype) {
+    case HGA_RAW_F64: return chanmap_launch_g<double>(m, a, smem, st);
+    case HGA_RAW_F32: return chanmap_launch_g<float>(m, a, smem, st);
+    case HGA_RAW_I32: return chanmap_launch_g<int32_t>(m, a, smem, st);
+    default: return chanmap_launch_g<int16_t>(m, a, smem, st);
+  }
+}
+extern "C" int hga_chanmap_apply(hga_chanmap* m, const double* x_dev, int64_t T, int64_t ldx, double* out_dev, int64_t ldo, void* stream) {
+  return hga_chanmap_apply_raw(m, x_dev, HGA_RAW_F64, nullptr, T, ldx, out_dev, ldo, stream);
 }
 extern "C" int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int64_t T, int64_t ldx, double* out_host, int64_t ldo) {
   if (!m || !x_host || !out_host) return fail(HGA_ERR_INVALID, "null argument");
@@ -1320,15 +1340,28 @@ extern "C" int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int6
 // ------------------------------------------------------------------------------------------------ offline, host buffers
 // Upload x in time slabs on the copy stream; after each slab, launch the work items whose rows are resident; download
 // each group's frame rows on the handle's own stream while the next slab uploads.
-extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
-                                        const int64_t* seg_len, const int64_t* out_row, const double* mu_host, const double* sigma_host,
-                                        double* out_host, int64_t ldo) {
-  if (!h || !x_host || !out_host || !seg_start || !seg_len || !out_row) return fail(HGA_ERR_INVALID, "null argument");
+//
+// Raw ingest (map != nullptr): the host rows are amplifier counts of `dtype`, c_in columns wide; each slab is uploaded at its
+// raw element size and expanded on the copy stream by the channel-map kernel (signal * gain, then the folded
+// pre-transform chain) into the float64 rows the extraction kernels read.
+static size_t raw_elem_size(int32_t dtype) { return dtype == HGA_RAW_F64 ? 8 : dtype == HGA_RAW_I16 ? 2 : 4; }
+
+static int extract_offline_host_impl(hga_handle* h, hga_chanmap* map, const void* x_host_v, int32_t dtype, const double* gain_host, int64_t ldx,
+                                     int32_t n_segments, const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
+                                     const double* mu_host, const double* sigma_host, double* out_host, int64_t ldo) {
+  if (!h || !x_host_v || !out_host || !seg_start || !seg_len || !out_row) return fail(HGA_ERR_INVALID, "null argument");
   const int C = h->cfg.n_channels, L = h->cfg.frame_len, hop = h->cfg.hop;
-  if (ldx < C || ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  const int c_in = map ? map->c_in : C;
+  if (map && (map->c_out != C || map->device != h->cfg.device))
+    return fail(HGA_ERR_INVALID, "channel map yields %d columns on device %d, the extractor wants %d on device %d", map->c_out, map->device, C, h->cfg.device);
+  if (dtype < HGA_RAW_F64 || dtype > HGA_RAW_I16) return fail(HGA_ERR_INVALID, "unknown raw dtype %d", dtype);
+  if (ldx < c_in || ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
   if (n_segments < 1) return HGA_OK;
   CU(cudaSetDevice(h->cfg.device));
   int rc;
+  const size_t esz = raw_elem_size(dtype), raw_row = (size_t)c_in * esz;
+  const unsigned char* x_raw = static_cast<const unsigned char*>(x_host_v);
+  const double* x_host = static_cast<const double*>(x_host_v);   // the plain float64 path (map == nullptr)
   int64_t lo = INT64_MAX, hi = 0, olo = INT64_MAX, ohi = 0;
   for (int i = 0; i < n_segments; ++i) {
     if (seg_len[i] < L) return fail(HGA_ERR_INVALID, "segment %d has %lld rows < frame_len %d", i, (long long)seg_len[i], L);
@@ -1345,9 +1378,32 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
   double* xd = h->xdev.as<double>() - lo * C;     // device row r <-> host row r
   double* od = h->outdev.as<double>() - olo * C;  // device out row r <-> host out row r
   const bool fused = (h->cfg.precision == HGA_PREC_F64 || h->cfg.precision == HGA_PREC_F32) && h->nb > 0;
+  const double* gain_d = nullptr;
+  if (map) {
+    if ((rc = h->rawdev.reserve((size_t)(hi - lo) * raw_row + (gain_host ? (size_t)c_in * 8 : 0) + 16))) return rc;
+    if (gain_host) {
+      const size_t off = ((size_t)(hi - lo) * raw_row + 15) / 16 * 16;
+      gain_d = reinterpret_cast<const double*>(static_cast<unsigned char*>(h->rawdev.p) + off);
+      CU(cudaMemcpyAsync(const_cast<double*>(gain_d), gain_host, (size_t)c_in * 8, cudaMemcpyHostToDevice, sc));
+    }
+  }
+  // rows [r0, r1) of the host recording -> float64 device rows, enqueued on stream st
+  auto upload = [&](int64_t r0, int64_t r1, cudaStream_t st) -> int {
+    if (!map) {
+      CU(cudaMemcpy2DAsync(xd + r0 * C, row_bytes, x_host + r0 * ldx, (size_t)ldx * 8, row_bytes, (size_t)(r1 - r0), cudaMemcpyHostToDevice, st));
+      return HGA_OK;
+    }
+    unsigned char* rd = static_cast<unsigned char*>(h->rawdev.p) + (size_t)(r0 - lo) * raw_row;
+    if (ldx == c_in)   // contiguous rows: one linear copy (a 2-D copy of 256 B rows runs at about half the link rate)
+      CU(cudaMemcpyAsync(rd, x_raw + (size_t)r0 * raw_row, (size_t)(r1 - r0) * raw_row, cudaMemcpyHostToDevice, st));
+    else
+      CU(cudaMemcpy2DAsync(rd, raw_row, x_raw + (size_t)r0 * ldx * esz, (size_t)ldx * esz, raw_row, (size_t)(r1 - r0), cudaMemcpyHostToDevice, st));
+    return hga_chanmap_apply_raw(map, rd, dtype, gain_d, r1 - r0, c_in, xd + r0 * C, C, st);
+  };
 
   if (!fused) {
-    CU(cudaMemcpy2DAsync(xd + lo * C, row_bytes, x_host + lo * ldx, (size_t)ldx * 8, row_bytes, (size_t)(hi - lo), cudaMemcpyHostToDevice, sk));
+    if (map) CU(cudaStreamSynchronize(sc));   // the gain vector went up on the copy stream
+    if ((rc = upload(lo, hi, sk))) return rc;
     if ((rc = extract_offline_dev(h, xd, C, n_segments, seg_start, seg_len, out_row, mu_d, sig_d, od, C, sk, nullptr, nullptr))) return rc;
     CU(cudaMemcpy2DAsync(out_host + olo * ldo, (size_t)ldo * 8, od + olo * C, row_bytes, row_bytes, (size_t)(ohi - olo), cudaMemcpyDeviceToHost, sk));
     CU(cudaStreamSynchronize(sk));
@@ -1374,7 +1430,11 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
   const int variant = h->plan_variant;
   const std::vector<Work>& W = h->work_host;
   const int64_t total_bytes = (hi - lo) * (int64_t)row_bytes;
-  int64_t slab_bytes = std::min<int64_t>(std::max<int64_t>(total_bytes / 12, 16LL << 20), 512LL << 20);
+  // Each slab's launch runs its share of the items at the full per-item duration, so S slabs cost about S x (whole-job kernel
+  // time) on the kernel stream; that hides behind the upload only while S <~ (upload time) / (kernel time) = about 3.8 x the
+  // element size at 52 GB/s and 200 G channel-samples/s.  float64: 12 slabs; int16 counts: 5.
+  const int64_t max_slabs = map ? std::max<int64_t>(2, std::min<int64_t>(12, (int64_t)(2.7 * (double)esz))) : 12;
+  int64_t slab_bytes = std::min<int64_t>(std::max<int64_t>(total_bytes / max_slabs, 16LL << 20), (512LL << 20) * 8 / (int64_t)esz);
   const int64_t slab_rows = std::max<int64_t>(hop, slab_bytes / (int64_t)row_bytes / hop * hop);
   const size_t n_slabs = (size_t)((hi - lo + slab_rows - 1) / slab_rows);
   while (h->slab_ev.size() < 2 * n_slabs + 2) {
@@ -1385,7 +1445,7 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
   size_t next = 0, ev = 0;
   for (int64_t r0 = lo; r0 < hi; r0 += slab_rows) {
     const int64_t r1 = std::min(hi, r0 + slab_rows);
-    CU(cudaMemcpy2DAsync(xd + r0 * C, row_bytes, x_host + r0 * ldx, (size_t)ldx * 8, row_bytes, (size_t)(r1 - r0), cudaMemcpyHostToDevice, sc));
+    if ((rc = upload(r0, r1, sc))) return rc;
     size_t end = next;
     while (end < W.size() && W[end].row0 + W[end].t_end <= r1 && W[end].row0 + W[end].t_begin >= lo) ++end;
     if (r1 == hi) end = W.size();
@@ -1415,4 +1475,15 @@ extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int
   CU(cudaStreamSynchronize(sk));
   CU(cudaStreamSynchronize(sc));
   return HGA_OK;
+}
+extern "C" int hga_extract_offline_host(hga_handle* h, const double* x_host, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
+                                        const int64_t* seg_len, const int64_t* out_row, const double* mu_host, const double* sigma_host,
+                                        double* out_host, int64_t ldo) {
+  return extract_offline_host_impl(h, nullptr, x_host, HGA_RAW_F64, nullptr, ldx, n_segments, seg_start, seg_len, out_row, mu_host, sigma_host, out_host, ldo);
+}
+extern "C" int hga_extract_offline_raw_host(hga_handle* h, hga_chanmap* map, const void* x_host, int32_t dtype, const double* gain_host, int64_t ldx,
+                                            int32_t n_segments, const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
+                                            const double* mu_host, const double* sigma_host, double* out_host, int64_t ldo) {
+  if (!map) return fail(HGA_ERR_INVALID, "null argument");
+  return extract_offline_host_impl(h, map, x_host, dtype, gain_host, ldx, n_segments, seg_start, seg_len, out_row, mu_host, sigma_host, out_host, ldo);
 }

@@ -24,7 +24,8 @@
 namespace hga {
 
 struct ChanMapArgs {
-  const double* x;
+  const void* x;         // [T, ldx] of IN (double for the transforms; float / int32 / int16 for raw amplifier counts)
+  const double* gain;    // [C_in] per-column factor applied at the load (GAIN variants), else unused
   int64_t ldx, T;
   int C_in, C_out, n_groups, n_idx;
   const int32_t* sel;    // [C_out] raw column of the direct term (-1: none)
@@ -51,6 +52,9 @@ __host__ __device__ inline size_t chanmap_smem_bytes(int C_in, int C_out, int n_
   return chanmap_table_bytes(C_out, n_groups, n_idx) + (size_t)kChanMapWarps * kChanMapRows * (C_in + n_groups) * 8;
 }
 
+// IN / GAIN: the load stage of the raw-ingest variant, `BCI2000MatFile.signals()` = `signal * gain`
+// (/root/reference/local/common.py:456-459): double(x[t, c]) * gain[c], one rounding like numpy's promoted product.
+template <typename IN, bool GAIN>
 __global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_constant__ ChanMapArgs a) {
   extern __shared__ __align__(16) unsigned char smem_cm[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -76,9 +80,13 @@ __global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_
 #pragma unroll
     for (int r = 0; r < kChanMapRows; ++r)
       if (r < nr) {
-        const double* xr = a.x + (t0 + r) * a.ldx;
+        const IN* xr = static_cast<const IN*>(a.x) + (t0 + r) * a.ldx;
         double* row = rows + r * rstride;
-        for (int c = lane; c < a.C_in; c += 32) row[c] = xr[c];
+        if constexpr (GAIN) {
+          for (int c = lane; c < a.C_in; c += 32) row[c] = (double)xr[c] * __ldg(a.gain + c);
+        } else {
+          for (int c = lane; c < a.C_in; c += 32) row[c] = (double)xr[c];
+        }
       }
     __syncwarp();
     // group means: the n_groups x kChanMapRows sums are reduced side by side, each by a segment of W lanes (W = the

@@ -166,6 +166,39 @@ class HgaEngine:
                                                  out.ctypes.data, out.strides[0] // 8))
         return out
 
+    def extract_offline_raw(self, raw, chanmap, gain=None, segments=None, mu=None, sigma=None, out=None):
+        """`extract_offline` of `chanmap(raw * gain)` for a HOST recording of raw amplifier counts (numpy int16 / int32 /
+        float32 / float64, (T, chanmap.spec.c_in)): slabs are uploaded at the raw element size and expanded on the device
+        (BCI2000MatFile.signals(), local/common.py:456-459, then the folded pre-transform chain).  chanmap: a
+        `transforms.ChannelMap` on this engine's device whose output width is the engine's channel count."""
+        from .transforms import RAW_NUMPY
+
+        raw = np.asarray(raw)
+        if raw.ndim != 2 or raw.shape[1] != chanmap.spec.c_in:
+            raise ValueError(f"expected (T, {chanmap.spec.c_in}) raw data, got {raw.shape}")
+        if raw.dtype not in RAW_NUMPY:
+            raise TypeError(f"raw element type {raw.dtype} is not one of float64, float32, int32, int16")
+        if chanmap.spec.c_out != self.n_channels or chanmap.device != self.device:
+            raise ValueError("channel map output width / device do not match the engine")
+        if raw.strides[1] != raw.itemsize or raw.strides[0] % raw.itemsize or raw.strides[0] < raw.shape[1] * raw.itemsize:
+            raw = np.ascontiguousarray(raw)
+        g = None
+        if gain is not None:
+            g = np.ascontiguousarray(np.broadcast_to(np.asarray(gain, dtype=np.float64).reshape(-1), (raw.shape[1],)))
+        start, length, frames, out_row = self._segments(raw.shape[0], segments)
+        total = int(sum(frames))
+        if out is None:
+            out = np.empty((total, self.n_channels), dtype=np.float64)
+        mu_h, sg_h = _musigma_host(mu, sigma, self.n_channels)
+        (_, ps), (_, pl), (_, po) = a1, a2, a3 = _vec_i64(start), _vec_i64(length), _vec_i64(out_row)
+        check(self._lib.hga_extract_offline_raw_host(self._h, chanmap._h, raw.ctypes.data, RAW_NUMPY[raw.dtype],
+                                                     g.ctypes.data if g is not None else None, raw.strides[0] // raw.itemsize,
+                                                     len(start), ps, pl, po,
+                                                     mu_h.ctypes.data if mu_h is not None else None,
+                                                     sg_h.ctypes.data if sg_h is not None else None,
+                                                     out.ctypes.data, out.strides[0] // 8))
+        return out
+
     # -- streaming -------------------------------------------------------------------------------------------------
     def push(self, x, mu=None, sigma=None):
         """`extract_features` of the long-lived extractor on the next n rows (local/units.py:151-160)."""

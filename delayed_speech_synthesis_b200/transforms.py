@@ -136,6 +136,27 @@ def fold(transforms: Optional[Sequence[Callable]], c_in: int) -> Optional[Channe
 
 
 # ---------------------------------------------------------------------------------------------- device object
+class _RawDtypes(dict):
+    """torch dtype -> HGA_RAW_* code of include/hga_b200.h (built on first use: torch is imported lazily here)."""
+
+    def _fill(self):
+        if not self:
+            import torch
+            self.update({torch.float64: 0, torch.float32: 1, torch.int32: 2, torch.int16: 3})
+
+    def __contains__(self, k):
+        self._fill()
+        return dict.__contains__(self, k)
+
+    def __getitem__(self, k):
+        self._fill()
+        return dict.__getitem__(self, k)
+
+
+RAW_DTYPES = _RawDtypes()
+RAW_NUMPY = {np.dtype(np.float64): 0, np.dtype(np.float32): 1, np.dtype(np.int32): 2, np.dtype(np.int16): 3}
+
+
 class ChannelMap:
     """A folded chain on one device: `apply(x)` for (T, c_in) float64 numpy arrays or torch CUDA tensors."""
 
@@ -191,6 +212,32 @@ class ChannelMap:
         res = np.empty((x.shape[0], self.spec.c_out), dtype=np.float64) if out is None else out
         check(lib.hga_chanmap_apply_host(self._h, x.ctypes.data, x.shape[0], x.shape[1], res.ctypes.data, res.shape[1]))
         return res
+
+    def apply_raw(self, x, gain=None, out=None):
+        """The map over raw amplifier counts: a CUDA (T, c_in) tensor of float64 / float32 / int32 / int16, each column
+        scaled by `gain` (scalar or (c_in,), float64) at the load -- `BCI2000MatFile.signals()` = `signal * gain`
+        (local/common.py:456-459) fused in front of the chain.  Returns a float64 (T, c_out) CUDA tensor."""
+        import torch
+
+        lib = _lib.load()
+        if not isinstance(x, torch.Tensor) or not x.is_cuda or x.dim() != 2 or x.shape[1] != self.spec.c_in:
+            raise ValueError(f"expected a CUDA (T, {self.spec.c_in}) tensor")
+        if x.dtype not in RAW_DTYPES:
+            raise TypeError(f"raw element type {x.dtype} is not one of float64, float32, int32, int16")
+        if x.stride(1) != 1:
+            x = x.contiguous()
+        g = None
+        if gain is not None:
+            g = np.broadcast_to(np.asarray(gain, dtype=np.float64).reshape(-1), (self.spec.c_in,))
+            g = torch.from_numpy(np.array(g)).to(x.device)
+        T = x.shape[0]
+        if out is None:
+            out = torch.empty((T, self.spec.c_out), dtype=torch.float64, device=x.device)
+        with torch.cuda.device(self.device):
+            check(lib.hga_chanmap_apply_raw(self._h, x.data_ptr(), RAW_DTYPES[x.dtype], None if g is None else g.data_ptr(), T,
+                                            max(x.stride(0), self.spec.c_in), out.data_ptr(), out.stride(0),
+                                            int(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class _MapBacked:

@@ -190,7 +190,24 @@ int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, const int32_
 int hga_chanmap_destroy(hga_chanmap* m);
 int hga_chanmap_apply(hga_chanmap* m, const double* x_dev, int64_t T, int64_t ldx, double* out_dev, int64_t ldo,
                       void* stream);
+/* Raw ingest: the same map applied to amplifier counts of another element type, each column scaled at the load,
+ * double(x[t, c]) * gain[c] -- `BCI2000MatFile.signals()` = `signal * gain` (/root/reference/local/common.py:456-459)
+ * without materialising the float64 recording on the host: the upload is the raw element size.  x_dev: [T, ldx]
+ * elements of `dtype`; gain_dev: [c_in] float64 in device memory, or NULL for no scaling. */
+enum { HGA_RAW_F64 = 0, HGA_RAW_F32 = 1, HGA_RAW_I32 = 2, HGA_RAW_I16 = 3 };
+int hga_chanmap_apply_raw(hga_chanmap* m, const void* x_dev, int32_t dtype, const double* gain_dev, int64_t T, int64_t ldx,
+                          double* out_dev, int64_t ldo, void* stream);
 int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int64_t T, int64_t ldx, double* out_host, int64_t ldo);
+/* hga_extract_offline_host fed with raw amplifier counts: x_host is [rows, ldx] elements of `dtype` (HGA_RAW_*), map->c_in
+ * columns wide; every upload slab travels at the raw element size and is expanded on the device, double(x) * gain[c]
+ * followed by the map (identity, or the folded selection / CAR chain), into the float64 rows the extraction reads.  This is
+ * `FeatureExtractionPipeline.get_features(BCI2000MatFile.signals(), trial_indices)` (/root/reference/prepare_corpus.py:42-52,
+ * local/common.py:456-459) without the float64 recording ever existing on the host.  gain_host: [c_in] float64 or NULL.
+ * Everything else as hga_extract_offline_host. */
+int hga_extract_offline_raw_host(hga_handle* h, hga_chanmap* map, const void* x_host, int32_t dtype, const double* gain_host,
+                                 int64_t ldx, int32_t n_segments, const int64_t* seg_start, const int64_t* seg_len,
+                                 const int64_t* out_row, const double* mu_host, const double* sigma_host, double* out_host,
+                                 int64_t ldo);
 
 /* ---- introspection for bench.py / tests ------------------------------------------------------------------------- */
 /* Kernel launches issued through this library by the calling process since load (all handles). */

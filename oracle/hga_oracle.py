@@ -383,3 +383,10 @@ def pack_packet(payload: np.ndarray) -> bytes:
     import struct
     payload = np.asarray(payload)
     return struct.pack('=BBB HH', 4, 1, 2, payload.shape[0], payload.shape[1]) + np.ascontiguousarray(payload, dtype=np.float32).tobytes()
+
+
+def scaled_signals(signal, gain):
+    """`BCI2000MatFile.signals()` (/root/reference/local/common.py:456-459): `signal * gain` with numpy's promotion --
+    raw counts (any real dtype) times the per-channel float64 `SourceChGain` vector (or a scalar)."""
+    return np.asarray(signal) * np.asarray(gain)
+

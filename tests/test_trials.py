@@ -69,3 +69,120 @@ def test_extract_trials_with_transform_chains():
     assert got.shape == want.shape and np.abs(got - want).max() <= 1e-9
     got_cb = corpus.extract_trials(ecog, TRIALS, fs, 64, pre_o, post_o)       # arbitrary callables: called per trial
     assert got_cb.shape == want.shape and np.abs(got_cb - want).max() <= 1e-9
+
+
+# ------------------------------------------------------------------------------------------------ raw ingest (signal * gain)
+def _raw_recording(T, C, dtype, seed):
+    rng = np.random.Generator(np.random.Philox(key=[20241104, seed]))
+    if np.issubdtype(dtype, np.integer):
+        lim = min(np.iinfo(dtype).max, 30000)
+        signal = rng.integers(-lim, lim, size=(T, C)).astype(dtype)
+    else:
+        signal = (rng.standard_normal((T, C)) * 3000.0).astype(dtype)
+    gain = rng.uniform(0.02, 0.3, size=C)                 # uV per count, per channel (SourceChGain)
+    return signal, gain
+
+
+def test_mat_wrapper_reads_what_the_reference_wrapper_reads(tmp_path):
+    """`BCI2000MatFile` (local/common.py:399-470) on a file written with the same field layout."""
+    from scipy.io import savemat
+
+    signal, gain = _raw_recording(200, 8, np.int16, 40)
+    savemat(tmp_path / "KeywordReading_01.mat", {
+        "signal": signal, "bad_channels": np.array(["chan3", "chan17"], dtype=object), "contaminated_electrodes": np.array([5, 6]),
+        "parameters": {"SamplingRate": {"NumericValue": 1000}, "SourceChGain": {"NumericValue": gain}},
+        "states": {"StimulusCode": np.repeat([0, 3, 0, 1, 0], 40).astype(np.uint8)}})
+    f = corpus.BCI2000MatFile(str(tmp_path / "KeywordReading_01.mat"))
+    assert f.fs == 1000 and f.bad_channels() == [3, 17] and f.contaminated_channels() == [5, 6]
+    assert f.ordered_stimulus_codes() == [1, 3]
+    raw, g = f.raw()
+    assert raw.dtype == np.int16 and np.array_equal(raw, signal) and np.array_equal(g, gain)
+    s = f.signals()
+    assert s.dtype == np.float64 and np.array_equal(s, O.scaled_signals(signal, gain))
+    assert np.array_equal(s, signal.astype(np.float64) * gain[None, :])
+
+
+def test_raw_widening_is_lossless():
+    for dt, want in ((np.uint8, np.int16), (np.int8, np.int16), (np.uint16, np.int32), (np.int64, np.float64), (np.float32, np.float32)):
+        a = np.arange(6, dtype=dt).reshape(3, 2)
+        b = corpus._raw_supported(a)
+        assert b.dtype == want and np.array_equal(a, b)
+    with pytest.raises(TypeError):
+        corpus._raw_supported(np.zeros((2, 2), dtype=np.complex128))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.int16, np.int32, np.float32, np.float64])
+def test_raw_ingest_is_bit_exact(dtype):
+    import torch
+    from delayed_speech_synthesis_b200 import transforms as TR
+
+    signal, gain = _raw_recording(1031, 128, dtype, 41)
+    want = O.scaled_signals(signal, gain)
+    m = TR.ChannelMap(TR.ChannelMapSpec.identity(128))
+    xd = torch.from_numpy(signal).cuda()
+    assert np.array_equal(m.apply_raw(xd, gain).cpu().numpy(), want)
+    assert np.array_equal(m.apply_raw(xd, 0.25).cpu().numpy(), O.scaled_signals(signal, 0.25))        # scalar gain
+    assert np.array_equal(m.apply_raw(xd).cpu().numpy(), signal.astype(np.float64))                   # no gain
+    sel = np.arange(127, -1, -2)
+    ms = TR.ChannelMap(TR.fold([TR.ChannelSelection(sel)], 128))
+    assert np.array_equal(ms.apply_raw(xd, gain).cpu().numpy(), want[:, sel])
+    with pytest.raises(TypeError):
+        m.apply_raw(xd.to(torch.int64), gain)
+
+
+@pytest.mark.gpu
+def test_extract_trials_from_raw_counts():
+    from delayed_speech_synthesis_b200 import transforms as TR
+
+    fs, C = 1000, 128
+    signal, gain = _raw_recording(6000, C, np.int16, 42)
+    ecog = O.scaled_signals(signal, gain)
+    want = oracle_get_features(ecog, TRIALS, fs, C)
+    got = corpus.extract_trials(signal, TRIALS, fs, C, gain=gain)
+    assert got.shape == want.shape and np.abs(got - want).max() <= 1e-9
+    assert np.array_equal(got, corpus.extract_trials(ecog, TRIALS, fs, C))                            # same bits as the float64 upload
+    sel = np.arange(0, 128, 2)
+    want_s = oracle_get_features(ecog, TRIALS, fs, 64, pre=[lambda d: O.select_columns(d, sel)])
+    got_s = corpus.extract_trials(signal, TRIALS, fs, 64, pre_transforms=[TR.ChannelSelection(sel)], gain=gain)
+    assert np.abs(got_s - want_s).max() <= 1e-9
+    got_cb = corpus.extract_trials(signal, TRIALS, fs, 64, pre_transforms=[lambda d: d[:, sel]], gain=gain)   # unfoldable chain
+    assert np.abs(got_cb - want_s).max() <= 1e-9
+    with pytest.raises(ValueError):
+        corpus.extract_trials(signal, TRIALS, fs, C, gain=np.ones(7))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+def test_offline_raw_host_slabs_match_float64_upload(dtype):
+    """hga_extract_offline_raw_host == hga_extract_offline_host on signal * gain, bit for bit (same kernels, same rows),
+    across several upload slabs, with a folded selection and the offline z-score."""
+    from delayed_speech_synthesis_b200 import transforms as TR
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+
+    fs, C = 1000, 128
+    T = 400_000                                                      # > one 16 MiB float64 slab
+    signal, gain = _raw_recording(T, C, dtype, 43)
+    ecog = O.scaled_signals(signal, gain)
+    mu, sigma = np.linspace(1.0, 2.0, C), np.linspace(0.5, 1.5, C)
+    eng = HgaEngine(fs, C)
+    ident = TR.ChannelMap(TR.ChannelMapSpec.identity(C), eng.device)
+    segs = [(0, 150_000), (150_000, 150_060), (150_100, T)]
+    want = eng.extract_offline(ecog, segs, mu, sigma)
+    got = eng.extract_offline_raw(signal, ident, gain, segs, mu, sigma)
+    assert got.shape == want.shape and np.array_equal(got, want)
+    ref = O.HighGammaExtractor(fs, C, post_transforms=[O.ZScoreNormalization(mu, sigma)]).extract_features(ecog[:3000])
+    assert np.abs(got[:len(ref)] - ref).max() <= 1e-9
+    # strided host rows (a column block of a wider file) and a folded selection
+    wide = np.zeros((T, C + 6), dtype=dtype)
+    wide[:, :C] = signal
+    assert np.array_equal(eng.extract_offline_raw(wide[:, :C], ident, gain, segs, mu, sigma), want)
+    sel = np.arange(0, C, 2)
+    eng64 = HgaEngine(fs, 64)
+    m = TR.ChannelMap(TR.fold([TR.ChannelSelection(sel)], C), eng64.device)
+    want_s = eng64.extract_offline(np.ascontiguousarray(ecog[:, sel]), segs)
+    assert np.array_equal(eng64.extract_offline_raw(signal, m, gain, segs), want_s)
+    with pytest.raises(ValueError):
+        eng.extract_offline_raw(signal, m, gain, segs)               # map width != engine width
+    with pytest.raises(TypeError):
+        eng.extract_offline_raw(signal.astype(np.int64), ident, gain, segs)

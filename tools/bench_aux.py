@@ -45,6 +45,16 @@ for name, ch, c_out in (("select+CAR+select 128->64", chain, 64), ("select+CAR 1
     s = timed(lambda: m.apply(x, out=o))
     gb = T * 8 * (C + c_out) / s / 1e9
     out[name] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}
+gain = np.linspace(0.02, 0.3, C)
+ident = TR.ChannelMap(TR.ChannelMapSpec.identity(C))
+o = torch.empty((T, C), dtype=torch.float64, device="cuda")
+for dt, nb in ((torch.int16, 2), (torch.float32, 4)):
+    raw = (x * 1000).to(dt)
+    s = timed(lambda: ident.apply_raw(raw, gain, out=o))
+    gb = T * C * (nb + 8) / s / 1e9
+    out[f"raw ingest signal*gain {str(dt).split('.')[-1]} -> f64 128->128"] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}
+    del raw
+del o
 f = torch.randn((360_000 * 8, C), dtype=torch.float64, device="cuda")   # features of 8 one-hour sessions
 st = ChannelStats(C, 0)
 s = timed(lambda: ChannelStats(C, 0).update(f))
