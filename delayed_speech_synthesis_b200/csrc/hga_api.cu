@@ -442,6 +442,11 @@ static int launch_pipe(const Cascade& q, const PipeOperands& po, int precision, 
   }
   return precision == HGA_PREC_F32 ? pipe_dispatch<f32x2>(q, pc, a, a.hop, tm, st, nullptr) : pipe_dispatch<double>(q, pc, a, a.hop, tm, st, nullptr);
 }
+// HGA_B200_FRAMES_ROLL=0 selects the per-window kernel (k_frames_seq) for the regular geometry too (A/B and tests).
+static bool frames_roll_on() {
+  const char* e = getenv("HGA_B200_FRAMES_ROLL");
+  return !(e && e[0] == '0');
+}
 static int64_t pipe_item_slots(const Cascade& q, const PipeOperands& po, int precision, int hop, int n_sm, int C) {
   const PipeConst& pc = pipe_shape().ver == 2 ? po.pc2 : po.pc;
   int occ = 1;
@@ -759,8 +764,14 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
   LAUNCHED();
   if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; }
   if (n_seg > 65535) return fail(HGA_ERR_UNSUPPORTED, "more than 65535 segments per call");
-  dim3 g2((unsigned)cg, (unsigned)((maxF + kFramesPerBlock - 1) / kFramesPerBlock), (unsigned)n_seg);
-  k_frames_seq<<<g2, 256, 0, st>>>(y, C, 0, h->segs.as<Segment>(), Segment{}, n_seg, C, maxF, L, hop, nullptr, nullptr, h->cfg.eps, mu, sigma, out, ldo);
+  if (L == 5 * hop && frames_roll_on()) {
+    const int R = roll_run_length(maxF * n_seg, cg, h->n_sm);
+    dim3 g2((unsigned)cg, (unsigned)((maxF + (int64_t)R * kRollWarps - 1) / ((int64_t)R * kRollWarps)), (unsigned)n_seg);
+    k_frames_roll<5><<<g2, 32 * kRollWarps, 0, st>>>(y, C, h->segs.as<Segment>(), Segment{}, n_seg, C, hop, R, h->cfg.eps, mu, sigma, out, ldo);
+  } else {
+    dim3 g2((unsigned)cg, (unsigned)((maxF + kFramesPerBlock - 1) / kFramesPerBlock), (unsigned)n_seg);
+    k_frames_seq<<<g2, 256, 0, st>>>(y, C, 0, h->segs.as<Segment>(), Segment{}, n_seg, C, maxF, L, hop, nullptr, nullptr, h->cfg.eps, mu, sigma, out, ldo);
+  }
   LAUNCHED();
   if (rem_out) {
     for (int i = 0; i < n_seg; ++i)
@@ -1137,6 +1148,19 @@ extern "C" int hga_log_power(int32_t device, const double* data_dev, int64_t row
   if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
   CU(cudaSetDevice(device));
   if (n_frames <= 0) return HGA_OK;
+  if (!start_dev && zero_rows == 0 && frame_len == 5 * hop && frames_roll_on()) {
+    // the path's geometry: rolling sums, one load per sample (bit-identical to the per-window loop below)
+    int n_sm = 148;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+    const int cg = (C + 31) / 32, R = roll_run_length(n_frames, cg, n_sm);
+    const int64_t rows_used = (n_frames - 1) * hop + frame_len;   // exactly n_frames windows
+    dim3 gr((unsigned)cg, (unsigned)((n_frames + (int64_t)R * kRollWarps - 1) / ((int64_t)R * kRollWarps)), 1);
+    if (gr.y > 65535u) return fail(HGA_ERR_UNSUPPORTED, "too many frames in one call");
+    k_frames_roll<5><<<gr, 32 * kRollWarps, 0, (cudaStream_t)stream>>>(data_dev, ld, nullptr, Segment{0, rows_used, 0}, 1, C, hop, R, eps, mu_dev,
+                                                                       sigma_dev, out_dev, ldo);
+    LAUNCHED();
+    return HGA_OK;
+  }
   dim3 g((unsigned)((C + 31) / 32), (unsigned)((n_frames + 7) / 8), 1);
   if (g.y > 65535u * 64u) return fail(HGA_ERR_UNSUPPORTED, "too many frames in one call");
   // grid.y is limited to 65535: fold the excess into several launches

@@ -59,6 +59,65 @@ __global__ void __launch_bounds__(128) k_iir_seq(const __grid_constant__ Cascade
 // data[(r - zero_rows) * ld + c].  Per-segment batching: window w of segment s reads rows relative to seg.row0.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kFramesPerBlock = 8;   // 32 (a forward sweep of 4 windows per warp for L1 reuse) measured slower: 3.26 vs 1.72 ms on K2
+
+// Regular windows with L = NB * hop (the path's 50 ms / 10 ms geometry, NB = 5), no leading zero rows: a thread walks down
+// its channel over a run of R consecutive windows and keeps the NB overlapping windows' sums live in registers.  Every
+// sample is loaded and squared once and added to all NB sums -- each sum still receives its rows in row order starting from
+// 0.0, so the result is bit-identical to the per-window loop (k_frames_seq) and to the reference's `array_sum_and_power`.
+// Slot k of acc belongs to the window whose first hop-block b has b % NB == k; it is cleared when that block starts and
+// emitted NB - 1 blocks later.  Loads: 1 + (NB - 1) / R per sample instead of NB.
+constexpr int kRollWarps = 8;
+template <int NB>
+__global__ void __launch_bounds__(32 * kRollWarps) k_frames_roll(const double* __restrict__ data, int64_t ld, const Segment* __restrict__ segs,
+                                                                 Segment one, int n_segs, int C, int hop, int R, double eps,
+                                                                 const double* __restrict__ mu, const double* __restrict__ sigma,
+                                                                 double* __restrict__ out, int64_t ldo) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int seg = blockIdx.z;
+  if (c >= C || seg >= n_segs) return;
+  const Segment sg = segs ? segs[seg] : one;
+  const int L = NB * hop;
+  if (sg.T < L) return;
+  const int64_t F = (sg.T - L) / hop + 1;
+  const int64_t w0 = ((int64_t)blockIdx.y * kRollWarps + (threadIdx.x >> 5)) * R;
+  if (w0 >= F) return;
+  const int64_t n = min((int64_t)R, F - w0), nblk = n + NB - 1;
+  const double* dp = data + (sg.row0 + w0 * hop) * ld + c;
+  double* op = out + (sg.out_row0 + w0) * ldo + c;
+  const bool zs = mu != nullptr;
+  const double m = zs ? mu[c] : 0.0, sd = zs ? sigma[c] : 1.0;
+  double acc[NB];
+#pragma unroll
+  for (int k = 0; k < NB; ++k) acc[k] = 0.0;
+  for (int64_t b0 = 0; b0 < nblk; b0 += NB) {
+#pragma unroll
+    for (int k = 0; k < NB; ++k) {
+      const int64_t b = b0 + k;
+      if (b < nblk) {
+        acc[k] = 0.0;
+        const double* bp = dp + b * hop * ld;
+        for (int j0 = 0; j0 < hop; j0 += 10) {
+          double v[10];
+#pragma unroll
+          for (int u = 0; u < 10; ++u) v[u] = j0 + u < hop ? __ldg(bp + (int64_t)(j0 + u) * ld) : 0.0;   // + 0.0 leaves a sum as it is
+#pragma unroll
+          for (int u = 0; u < 10; ++u) {
+            const double sq = __dmul_rn(v[u], v[u]);
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc[q] = __dadd_rn(acc[q], sq);
+          }
+        }
+        const int64_t i = b - (NB - 1);
+        if (i >= 0) op[i * ldo] = feature(acc[(k + 1) % NB], (double)L, eps, zs, m, sd);
+      }
+    }
+  }
+}
+// run length: enough warps for two waves of 64 per SM, at most 128 windows (halo (NB - 1) / R <= 3 %), at least 16
+inline int roll_run_length(int64_t frames_total, int cg, int n_sm) {
+  const int64_t r = frames_total * cg / ((int64_t)n_sm * 128);
+  return (int)(r < 16 ? 16 : r > 128 ? 128 : r);
+}
 __global__ void __launch_bounds__(256) k_frames_seq(const double* __restrict__ data, int64_t ld, int64_t zero_rows,
                                                     const Segment* __restrict__ segs, Segment one, int n_segs, int C,
                                                     int64_t frames_per_seg_max, int L, int hop,

@@ -71,6 +71,25 @@ def test_log_power_matches_reference_function(rows, C, fs):
         assert _err(got, ref)[0] <= TOL_EXACT
 
 
+@pytest.mark.parametrize("rows,C,fs", [(60_000, 128, 1000), (7_777, 33, 2000), (50, 5, 1000), (1_290, 64, 1000), (200_013, 40, 1000)])
+def test_log_power_rolling_sums_are_bit_identical_to_the_window_loop(rows, C, fs, monkeypatch):
+    """k_frames_roll (one load per sample, five live sums) against k_frames_seq (thread per window) and the oracle's row-order
+    loop: every sum receives its rows in the same order, so the bits agree; with the fused z-score too."""
+    from delayed_speech_synthesis_b200 import ops
+    data = O.synthetic_ecog(rows, C, fs, "ecog", session=6)
+    mu, sigma = np.linspace(1.0, 2.0, C), np.linspace(0.5, 1.5, C)
+    roll = ops.log_power(data, fs, 0.05, 0.01)
+    roll_z = ops.log_power(data, fs, 0.05, 0.01, mu, sigma)
+    monkeypatch.setenv("HGA_B200_FRAMES_ROLL", "0")
+    seq = ops.log_power(data, fs, 0.05, 0.01)
+    seq_z = ops.log_power(data, fs, 0.05, 0.01, mu, sigma)
+    assert roll.shape == seq.shape == ((rows - int(0.05 * fs)) // int(0.01 * fs) + 1, C)
+    assert np.array_equal(roll, seq) and np.array_equal(roll_z, seq_z)
+    n = min(len(roll), 300)
+    ref = O.compute_log_power_features(data[:(n - 1) * int(0.01 * fs) + int(0.05 * fs)], fs, 0.05, 0.01)
+    assert _err(roll[:n], ref)[0] <= TOL_EXACT
+
+
 def test_log_power_strided_and_errors():
     from delayed_speech_synthesis_b200.hga_optimized import compute_log_power_features
     big = O.synthetic_ecog(400, 12, 1000, "white")
