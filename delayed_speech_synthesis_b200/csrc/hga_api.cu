@@ -299,15 +299,20 @@ static PipeShape pipe_shape(bool f32 = false) {
   }
   return p;
 }
+// true the first time the calling instantiation runs on the current device (a process may hold handles on several devices;
+// cudaFuncSetAttribute applies to the current device only)
+static bool first_use_on_device(std::atomic<uint64_t>& mask) {
+  int d = 0;
+  cudaGetDevice(&d);
+  const uint64_t bit = 1ull << (d & 63);
+  return !(mask.fetch_or(bit) & bit);
+}
 template <typename T, int S, int TB, int HOP>
 static int pipe_launch_t(const Cascade& q, const PipeConst& pc, const FusedArgs& a, const CUtensorMap& tm, cudaStream_t st, int* occ) {
   auto kern = k_hga_pipe<T, S, TB, HOP>;
   const int smem = (int)PipeSmem<S, TB, T>::total;
-  static bool attr_done = false;
-  if (!attr_done) {
-    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_done = true;
-  }
+  static std::atomic<uint64_t> attr_done{0};   // function attributes are per device: one bit per ordinal
+  if (first_use_on_device(attr_done)) CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   if (occ) {
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, 64 * S, smem));
     return HGA_OK;
@@ -330,11 +335,8 @@ static int pipe2_launch_am(const Cascade& q, const PipeConst& pc, const FusedArg
   constexpr bool kPerG = S == 4;
   auto kern = k_hga_pipe2<T, S, TB, HOP, kPipe2NF, kPerG, AM>;
   const int smem = (int)Pipe2Smem<S, TB, T>::total, threads = 32 * (S + kPipe2NF + 1);
-  static bool attr_done = false;
-  if (!attr_done) {
-    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_done = true;
-  }
+  static std::atomic<uint64_t> attr_done{0};   // function attributes are per device: one bit per ordinal
+  if (first_use_on_device(attr_done)) CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   if (occ) {
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kern, threads, smem));
     return HGA_OK;
@@ -1310,10 +1312,11 @@ extern "C" int hga_chanmap_destroy(hga_chanmap* m) {
 }
 template <typename IN, bool GAIN>
 static int chanmap_launch(hga_chanmap* m, const ChanMapArgs& a, size_t smem, cudaStream_t stream) {
-  static size_t smem_set = 0;  // per instantiation
-  if (smem > 48 * 1024 && smem > smem_set) {
+  static size_t smem_set[64] = {};  // per instantiation and device
+  size_t& set = smem_set[m->device & 63];
+  if (smem > 48 * 1024 && smem > set) {
     CU(cudaFuncSetAttribute(k_chanmap<IN, GAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
+    set = smem;
   }
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(smem, 1)));
   const int64_t need = (a.T + kChanMapWarps * kChanMapRows - 1) / (kChanMapWarps * kChanMapRows);
