@@ -186,3 +186,23 @@ def test_offline_raw_host_slabs_match_float64_upload(dtype):
         eng.extract_offline_raw(signal, m, gain, segs)               # map width != engine width
     with pytest.raises(TypeError):
         eng.extract_offline_raw(signal.astype(np.int64), ident, gain, segs)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["exact", "f32"])
+def test_offline_raw_host_other_precisions(precision):
+    """The raw host call in the exact mode (single upload, sequential kernels) and in float32 mode: same bits as the float64
+    host call of that mode on signal * gain."""
+    from delayed_speech_synthesis_b200 import transforms as TR
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+
+    fs, C, T = 1000, 64, 20_000
+    signal, gain = _raw_recording(T, C, np.int32, 44)
+    ecog = O.scaled_signals(signal, gain)
+    eng = HgaEngine(fs, C, precision=precision)
+    ident = TR.ChannelMap(TR.ChannelMapSpec.identity(C), eng.device)
+    segs = [(0, 12_000), (12_000, T)]
+    want = eng.extract_offline(ecog, segs)
+    got = eng.extract_offline_raw(signal, ident, gain, segs)
+    assert got.shape == want.shape and np.array_equal(got, want)
+    assert np.array_equal(eng.extract_offline_raw(signal, ident, None, segs), eng.extract_offline(signal.astype(np.float64), segs))
