@@ -1254,6 +1254,7 @@ struct hga_chanmap {
   const int32_t *sel = nullptr, *grp = nullptr, *gptr = nullptr, *gidx = nullptr;
   const double *alpha = nullptr, *beta = nullptr;
   DevBuf xdev, odev;  // staging of the host-buffer variant
+  bool identity = false;  // out[t, j] = x[t, j]: raw ingest takes the flat k_rawscale stream
 };
 
 extern "C" int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, const int32_t* sel, const int32_t* grp, const double* alpha,
@@ -1276,6 +1277,8 @@ extern "C" int hga_chanmap_create(int32_t device, int32_t c_in, int32_t c_out, c
   CU(cudaSetDevice(device));
   hga_chanmap* m = new hga_chanmap();
   m->device = device; m->c_in = c_in; m->c_out = c_out; m->n_groups = n_groups; m->n_idx = n_idx;
+  m->identity = c_in == c_out;
+  for (int j = 0; j < c_out && m->identity; ++j) m->identity = sel[j] == j && grp[j] < 0 && alpha[j] == 1.0;
   cudaDeviceGetAttribute(&m->n_sm, cudaDevAttrMultiProcessorCount, device);
   const size_t n_i32 = (size_t)2 * c_out + (n_groups + 1) + n_idx, off_d = (n_i32 * 4 + 15) / 16 * 16;
   std::vector<unsigned char> hbuf(off_d + (size_t)2 * c_out * 8, 0);
@@ -1330,6 +1333,32 @@ static int chanmap_launch_g(hga_chanmap* m, const ChanMapArgs& a, size_t smem, c
   return a.gain ? chanmap_launch<IN, true>(m, a, smem, stream) : chanmap_launch<IN, false>(m, a, smem, stream);
 }
 
+// Identity map over compact rows: the flat k_rawscale stream (HGA_B200_NO_RAWSCALE=1 keeps the row-wise kernel, for A/B runs).
+static bool rawscale_applies(const hga_chanmap* m, const void* x, int32_t dtype, const double* gain, int64_t ldx, const double* out, int64_t ldo) {
+  static const bool off = [] { const char* e = getenv("HGA_B200_NO_RAWSCALE"); return e && *e && *e != '0'; }();
+  if (off || !m->identity || ldx != m->c_in || ldo != m->c_out || (m->c_in & 3)) return false;
+  const size_t quad = 4 * (dtype == HGA_RAW_F64 ? 8 : dtype == HGA_RAW_I16 ? 2 : 4);
+  return ((uintptr_t)x % (quad > 16 ? 16 : quad)) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)gain & 15) == 0;
+}
+template <typename IN>
+static int rawscale_launch(hga_chanmap* m, const void* x, const double* gain, int64_t T, double* out, cudaStream_t stream) {
+  const int qpr = m->c_in / 4;
+  const int64_t n_quads = T * qpr;
+  // total threads a multiple of quads_per_row: each thread keeps its four gain factors in registers
+  int64_t q = qpr, t = kRawScaleThreads;
+  while (t) { const int64_t r = q % t; q = t; t = r; }   // q = gcd(qpr, threads)
+  const int64_t mult = qpr / q;
+  const int64_t need = (n_quads + (int64_t)kRawScaleThreads * kRawScaleUnroll - 1) / ((int64_t)kRawScaleThreads * kRawScaleUnroll);
+  int64_t grid = std::max<int64_t>(1, std::min<int64_t>(need, (int64_t)m->n_sm * 4));   // 56 registers: 4 CTAs per SM
+  grid = (grid + mult - 1) / mult * mult;
+  if (gain)
+    k_rawscale<IN, true><<<(unsigned)grid, kRawScaleThreads, 0, stream>>>(static_cast<const IN*>(x), gain, out, n_quads, qpr);
+  else
+    k_rawscale<IN, false><<<(unsigned)grid, kRawScaleThreads, 0, stream>>>(static_cast<const IN*>(x), nullptr, out, n_quads, qpr);
+  LAUNCHED();
+  return HGA_OK;
+}
+
 extern "C" int hga_chanmap_apply_raw(hga_chanmap* m, const void* x_dev, int32_t dtype, const double* gain_dev, int64_t T, int64_t ldx,
                                      double* out_dev, int64_t ldo, void* stream) {
   if (!m || !x_dev || !out_dev) return fail(HGA_ERR_INVALID, "null argument");
@@ -1341,6 +1370,14 @@ extern "C" int hga_chanmap_apply_raw(hga_chanmap* m, const void* x_dev, int32_t 
   const size_t smem = chanmap_smem_bytes(m->c_in, m->c_out, m->n_groups, m->n_idx);
   if (smem > 227 * 1024) return fail(HGA_ERR_UNSUPPORTED, "channel map needs %zu bytes of shared memory (c_in=%d c_out=%d)", smem, m->c_in, m->c_out);
   cudaStream_t st = (cudaStream_t)stream;
+  if (rawscale_applies(m, x_dev, dtype, gain_dev, ldx, out_dev, ldo)) {
+    switch (dtype) {
+      case HGA_RAW_F64: return rawscale_launch<double>(m, x_dev, gain_dev, T, out_dev, st);
+      case HGA_RAW_F32: return rawscale_launch<float>(m, x_dev, gain_dev, T, out_dev, st);
+      case HGA_RAW_I32: return rawscale_launch<int32_t>(m, x_dev, gain_dev, T, out_dev, st);
+      default: return rawscale_launch<int16_t>(m, x_dev, gain_dev, T, out_dev, st);
+    }
+  }
   switch (dtype) {
     case HGA_RAW_F64: return chanmap_launch_g<double>(m, a, smem, st);
     case HGA_RAW_F32: return chanmap_launch_g<float>(m, a, smem, st);

@@ -128,4 +128,67 @@ __global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_
   }
 }
 
+// K-rawscale: the identity channel map (raw ingest with no selection / re-referencing folded in), i.e. only
+// `BCI2000MatFile.signals()` = `signal * gain` (/root/reference/local/common.py:456-459): out[t, c] = double(x[t, c]) * gain[c].
+// A flat stream over T * C elements in groups of four: one 8 / 16 / 32 B load and two 16 B stores per group, four groups
+// per thread in flight.  The launch makes the total thread count a multiple of C / 4, so a thread's four columns (and its
+// four gain factors, kept in registers) never change.  Same product, same single rounding as k_chanmap<IN, GAIN>.
+// Bound: HBM, sizeof(IN) + 8 bytes per element.
+constexpr int kRawScaleThreads = 256;
+constexpr int kRawScaleUnroll = 4;
+struct RawQuadF64 { double2 a, b; };
+template <typename IN> struct RawQuad;
+template <> struct RawQuad<int16_t> { using type = short4; };
+template <> struct RawQuad<int32_t> { using type = int4; };
+template <> struct RawQuad<float> { using type = float4; };
+template <> struct RawQuad<double> { using type = RawQuadF64; };
+__device__ __forceinline__ short4 rawquad_load(const short4* p) { return __ldg(p); }
+__device__ __forceinline__ int4 rawquad_load(const int4* p) { return __ldg(p); }
+__device__ __forceinline__ float4 rawquad_load(const float4* p) { return __ldg(p); }
+__device__ __forceinline__ RawQuadF64 rawquad_load(const RawQuadF64* p) {
+  const double2* q = reinterpret_cast<const double2*>(p);
+  return RawQuadF64{__ldg(q), __ldg(q + 1)};
+}
+template <typename Q>
+__device__ __forceinline__ void rawquad_cvt(const Q& r, double (&d)[4]) {
+  d[0] = (double)r.x; d[1] = (double)r.y; d[2] = (double)r.z; d[3] = (double)r.w;
+}
+__device__ __forceinline__ void rawquad_cvt(const RawQuadF64& r, double (&d)[4]) {
+  d[0] = r.a.x; d[1] = r.a.y; d[2] = r.b.x; d[3] = r.b.y;
+}
+template <typename IN, bool GAIN>
+__global__ void __launch_bounds__(kRawScaleThreads, 4) k_rawscale(const IN* __restrict__ x, const double* __restrict__ gain,
+                                                                  double* __restrict__ out, int64_t n_quads, int quads_per_row) {
+  using Q = typename RawQuad<IN>::type;
+  const Q* xq = reinterpret_cast<const Q*>(x);
+  double2* oq = reinterpret_cast<double2*>(out);
+  const int64_t S = (int64_t)gridDim.x * kRawScaleThreads, tid = (int64_t)blockIdx.x * kRawScaleThreads + threadIdx.x;
+  double g[4] = {1.0, 1.0, 1.0, 1.0};
+  if constexpr (GAIN) {
+    const double2* gq = reinterpret_cast<const double2*>(gain) + 2 * (tid % quads_per_row);   // S % quads_per_row == 0
+    const double2 g0 = __ldg(gq), g1 = __ldg(gq + 1);
+    g[0] = g0.x; g[1] = g0.y; g[2] = g1.x; g[3] = g1.y;
+  }
+  auto emit = [&](int64_t i, const Q& r) {
+    double d[4];
+    rawquad_cvt(r, d);
+    if constexpr (GAIN) {
+      oq[2 * i] = make_double2(d[0] * g[0], d[1] * g[1]);
+      oq[2 * i + 1] = make_double2(d[2] * g[2], d[3] * g[3]);
+    } else {
+      oq[2 * i] = make_double2(d[0], d[1]);
+      oq[2 * i + 1] = make_double2(d[2], d[3]);
+    }
+  };
+  int64_t i = tid;
+  for (; i + (kRawScaleUnroll - 1) * S < n_quads; i += kRawScaleUnroll * S) {
+    Q r[kRawScaleUnroll];
+#pragma unroll
+    for (int j = 0; j < kRawScaleUnroll; ++j) r[j] = rawquad_load(xq + i + j * S);
+#pragma unroll
+    for (int j = 0; j < kRawScaleUnroll; ++j) emit(i + j * S, r[j]);
+  }
+  for (; i < n_quads; i += S) emit(i, rawquad_load(xq + i));
+}
+
 }  // namespace hga

@@ -132,6 +132,30 @@ def test_raw_ingest_is_bit_exact(dtype):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("C", [96, 1024, 6])
+def test_raw_ingest_flat_stream_matches_rowwise(C):
+    """The identity map over compact rows takes the flat k_rawscale stream (C % 4 == 0; 96 columns: 24 quads per row, so the
+    grid is rounded to a multiple of 3 CTAs to keep each thread on fixed columns); padded rows and C = 6 take the row-wise
+    k_chanmap.  Both must be `signal * gain` bit for bit (/root/reference/local/common.py:456-459)."""
+    import torch
+    from delayed_speech_synthesis_b200 import transforms as TR
+
+    T = 4099
+    signal, gain = _raw_recording(T, C, np.int16, 45)
+    want = O.scaled_signals(signal, gain)
+    m = TR.ChannelMap(TR.ChannelMapSpec.identity(C))
+    xd = torch.from_numpy(signal).cuda()
+    assert np.array_equal(m.apply_raw(xd, gain).cpu().numpy(), want)
+    assert np.array_equal(m.apply_raw(xd).cpu().numpy(), signal.astype(np.float64))
+    wide = torch.zeros((T, C + 4), dtype=torch.int16, device="cuda")
+    wide[:, :C] = xd
+    assert np.array_equal(m.apply_raw(wide[:, :C], gain).cpu().numpy(), want)
+    for dt in (np.float32, np.float64, np.int32):
+        sig, g = _raw_recording(517, C, dt, 46)
+        assert np.array_equal(m.apply_raw(torch.from_numpy(sig).cuda(), g).cpu().numpy(), O.scaled_signals(sig, g))
+
+
+@pytest.mark.gpu
 def test_extract_trials_from_raw_counts():
     from delayed_speech_synthesis_b200 import transforms as TR
 
