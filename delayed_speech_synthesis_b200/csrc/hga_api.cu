@@ -1338,7 +1338,7 @@ static bool rawscale_applies(const hga_chanmap* m, const void* x, int32_t dtype,
   static const bool off = [] { const char* e = getenv("HGA_B200_NO_RAWSCALE"); return e && *e && *e != '0'; }();
   if (off || !m->identity || ldx != m->c_in || ldo != m->c_out || (m->c_in & 3)) return false;
   const size_t quad = 4 * (dtype == HGA_RAW_F64 ? 8 : dtype == HGA_RAW_I16 ? 2 : 4);
-  return ((uintptr_t)x % (quad > 16 ? 16 : quad)) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)gain & 15) == 0;
+  return ((uintptr_t)x % (quad > 16 ? 16 : quad)) == 0 && ((uintptr_t)out & 31) == 0 && ((uintptr_t)gain & 15) == 0;
 }
 template <typename IN>
 static int rawscale_launch(hga_chanmap* m, const void* x, const double* gain, int64_t T, double* out, cudaStream_t stream) {

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(32 * kChanMapWarps, 8) k_chanmap(const __grid_
 
 // K-rawscale: the identity channel map (raw ingest with no selection / re-referencing folded in), i.e. only
 // `BCI2000MatFile.signals()` = `signal * gain` (/root/reference/local/common.py:456-459): out[t, c] = double(x[t, c]) * gain[c].
-// A flat stream over T * C elements in groups of four: one 8 / 16 / 32 B load and two 16 B stores per group, four groups
+// A flat stream over T * C elements in groups of four: one 8 / 16 / 32 B load and one 32 B store per group, four groups
 // per thread in flight.  The launch makes the total thread count a multiple of C / 4, so a thread's four columns (and its
 // four gain factors, kept in registers) never change.  Same product, same single rounding as k_chanmap<IN, GAIN>.
 // Bound: HBM, sizeof(IN) + 8 bytes per element.
@@ -161,7 +161,6 @@ __global__ void __launch_bounds__(kRawScaleThreads, 4) k_rawscale(const IN* __re
                                                                   double* __restrict__ out, int64_t n_quads, int quads_per_row) {
   using Q = typename RawQuad<IN>::type;
   const Q* xq = reinterpret_cast<const Q*>(x);
-  double2* oq = reinterpret_cast<double2*>(out);
   const int64_t S = (int64_t)gridDim.x * kRawScaleThreads, tid = (int64_t)blockIdx.x * kRawScaleThreads + threadIdx.x;
   double g[4] = {1.0, 1.0, 1.0, 1.0};
   if constexpr (GAIN) {
@@ -169,16 +168,15 @@ __global__ void __launch_bounds__(kRawScaleThreads, 4) k_rawscale(const IN* __re
     const double2 g0 = __ldg(gq), g1 = __ldg(gq + 1);
     g[0] = g0.x; g[1] = g0.y; g[2] = g1.x; g[3] = g1.y;
   }
+  // one 256-bit store per quad (st.global.v4.f64, sm_100): a warp writes 1 KB of whole lines per instruction.  Measured
+  // (tools/microbench/write_rates.cu, 3.69 GB of output): 2 x 16 B stores per quad 3.4 TB/s of writes, 32 B stores 6.3 TB/s.
   auto emit = [&](int64_t i, const Q& r) {
     double d[4];
     rawquad_cvt(r, d);
     if constexpr (GAIN) {
-      oq[2 * i] = make_double2(d[0] * g[0], d[1] * g[1]);
-      oq[2 * i + 1] = make_double2(d[2] * g[2], d[3] * g[3]);
-    } else {
-      oq[2 * i] = make_double2(d[0], d[1]);
-      oq[2 * i + 1] = make_double2(d[2], d[3]);
+      d[0] *= g[0]; d[1] *= g[1]; d[2] *= g[2]; d[3] *= g[3];
     }
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(out + 4 * i), "d"(d[0]), "d"(d[1]), "d"(d[2]), "d"(d[3]) : "memory");
   };
   int64_t i = tid;
   for (; i + (kRawScaleUnroll - 1) * S < n_quads; i += kRawScaleUnroll * S) {
