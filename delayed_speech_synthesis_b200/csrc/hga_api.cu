@@ -1194,6 +1194,15 @@ extern "C" int hga_zscore(int32_t device, const double* f_dev, int64_t F, int32_
   if (F == 0) return HGA_OK;
   int n_sm = 148;
   cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+  static const bool no_quad = [] { const char* e = getenv("HGA_B200_NO_ZSCORE4"); return e && *e && *e != '0'; }();
+  if (!no_quad && f_dev != out_dev && (C & 3) == 0 && (ld & 3) == 0 && (ldo & 3) == 0 &&
+      (((uintptr_t)f_dev | (uintptr_t)out_dev | (uintptr_t)mu_dev | (uintptr_t)sigma_dev) & 31) == 0) {
+    const unsigned cg4 = (unsigned)((C / 4 + 31) / 32);
+    const unsigned gy4 = (unsigned)std::max<int64_t>(1, std::min<int64_t>((F + 31) / 32, (int64_t)n_sm * 8 / cg4 + 1));
+    k_zscore4<<<dim3(cg4, gy4), 256, 0, (cudaStream_t)stream>>>(f_dev, F, C, ld, mu_dev, sigma_dev, out_dev, ldo);
+    LAUNCHED();
+    return HGA_OK;
+  }
   const unsigned cgz = (unsigned)((C + 31) / 32);
   const unsigned gy = (unsigned)std::max<int64_t>(1, std::min<int64_t>((F + 31) / 32, (int64_t)n_sm * 8 / cgz + 1));
   k_zscore<<<dim3(cgz, gy), 256, 0, (cudaStream_t)stream>>>(f_dev, F, C, ld, mu_dev, sigma_dev, out_dev, ldo);

@@ -175,6 +175,41 @@ __global__ void __launch_bounds__(256) k_zscore(const double* __restrict__ f, in
   for (; r < F; r += step) out[r * ldo + c] = __ddiv_rn(__dsub_rn(f[r * ld + c], m), sd);
 }
 
+// The same map with four adjacent channels per thread: one 256-bit load and one 256-bit store per row (ld / st.global.v4.f64;
+// a warp moves 1 KB of whole lines per instruction -- see tools/microbench/write_rates.cu for what the store width buys).
+// Needs C, ld, ldo multiples of 4 and 32 B-aligned f / out / mu / sigma; same IEEE operations per element, same bits.
+struct ZQuad { double v[4]; };
+__device__ __forceinline__ ZQuad zquad_load(const double* p) {
+  ZQuad q;
+  asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(q.v[0]), "=d"(q.v[1]), "=d"(q.v[2]), "=d"(q.v[3]) : "l"(p));
+  return q;
+}
+__device__ __forceinline__ void zquad_store(double* p, const ZQuad& q) {
+  asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(q.v[0]), "d"(q.v[1]), "d"(q.v[2]), "d"(q.v[3]) : "memory");
+}
+__global__ void __launch_bounds__(256) k_zscore4(const double* __restrict__ f, int64_t F, int C, int64_t ld, const double* __restrict__ mu,
+                                                 const double* __restrict__ sigma, double* __restrict__ out, int64_t ldo) {
+  const int c = (blockIdx.x * 32 + (threadIdx.x & 31)) * 4;
+  if (c >= C) return;
+  const ZQuad m = zquad_load(mu + c), sd = zquad_load(sigma + c);
+  auto z = [&](const ZQuad& v) {
+    ZQuad o;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o.v[k] = __ddiv_rn(__dsub_rn(v.v[k], m.v[k]), sd.v[k]);
+    return o;
+  };
+  const int64_t step = (int64_t)gridDim.y * 8;
+  int64_t r = (int64_t)blockIdx.y * 8 + (threadIdx.x >> 5);
+  for (; r + 3 * step < F; r += 4 * step) {
+    ZQuad v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = zquad_load(f + (r + j * step) * ld + c);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) zquad_store(out + (r + j * step) * ldo + c, z(v[j]));
+  }
+  for (; r < F; r += step) zquad_store(out + r * ldo + c, z(zquad_load(f + r * ld + c)));
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // K-stream: one launch per push = sosfilt x2 with carried state (units.py:151-152) + WarmStartFrameBuffer.insert
 // (pyx:96-131) + compute_log_power_features (pyx:27-47) + optional z-score.  Thread per channel; every thread owns

@@ -392,3 +392,21 @@ def test_zscore_callable_matches_numpy():
     rng = np.random.default_rng(2)
     f, mu, sd = rng.normal(size=(500, 64)), rng.normal(size=64), rng.uniform(0.2, 2, 64)
     assert np.array_equal(ZScoreNormalization(mu, sd)(f), (f - mu) / sd)
+
+
+@pytest.mark.parametrize("F,C", [(4099, 128), (517, 100), (33, 1024), (300, 6)])
+def test_zscore_quad_and_scalar_kernels_are_bit_exact(F, C):
+    """k_zscore4 (C % 4 == 0: four channels per thread, 256-bit loads / stores) and k_zscore (any C) against numpy's
+    (f - mu) / sigma, bit for bit (/root/reference/local/common.py:375-376); a row-padded input too."""
+    import torch
+    from delayed_speech_synthesis_b200 import ops
+    rng = np.random.default_rng(5)
+    f, mu, sd = rng.normal(size=(F, C)), rng.normal(size=C), rng.uniform(0.2, 2, C)
+    fd, mud, sdd = (torch.from_numpy(a).cuda() for a in (f, mu, sd))
+    assert np.array_equal(ops.zscore(fd, mud, sdd).cpu().numpy(), (f - mu) / sd)
+    wide = torch.zeros((F, C + 4), dtype=torch.float64, device="cuda")
+    wide[:, :C] = fd
+    assert np.array_equal(ops.zscore(wide[:, :C], mud, sdd).cpu().numpy(), (f - mu) / sd)
+    odd = torch.zeros((F, C + 3), dtype=torch.float64, device="cuda")
+    odd[:, :C] = fd
+    assert np.array_equal(ops.zscore(odd[:, :C], mud, sdd).cpu().numpy(), (f - mu) / sd)
