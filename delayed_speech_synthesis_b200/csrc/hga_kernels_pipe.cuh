@@ -19,6 +19,7 @@
 #pragma once
 #include <cuda.h>
 
+#include "hga_async.cuh"
 #include "hga_kernels_fused.cuh"
 
 namespace hga {
@@ -33,64 +34,6 @@ struct PipeConst {  // compile-time-indexable, warp-uniform operands (constant b
   unsigned amask;  // bit s set: section s has numerator [1, 0, -1] (3-slot form)
   int pad_;
 };
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
-// TMA: one (32 channels x TB rows) f64 box of x -> shared memory, completion on an mbarrier.  Out-of-range columns
-// (C not a multiple of 32) and rows past the end of x are zero-filled by the hardware.
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int row, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-          smem_u32(dst)),
-      "l"(map), "r"(c0), "r"(row), "r"(smem_u32(bar))
-      : "memory");
-}
-
-// Two float32 lanes in one 64-bit register (fma.rn.f32x2 / add.rn.f32x2, SASS FFMA2 / FADD2): one lane of a warp filters
-// TWO channels (c and c + 32) per instruction, which halves the issue slots of the float32 cascade.
-struct f32x2 {
-  unsigned long long v;
-};
-__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
-__device__ __forceinline__ f32x2 operator+(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
-  return r;
-}
-__device__ __forceinline__ f32x2 operator-(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
-  return r;
-}
-using ::fma;  // keep the scalar overloads visible next to the packed one
-__device__ __forceinline__ f32x2 fma(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
-  return r;
-}
 
 // Per-arithmetic traits: channels per lane, coefficient operands (warp-uniform constant-bank reads; a1 / a2 are stored
 // negated for the packed type, negated through the operand modifier otherwise), conversions at the tile boundaries.

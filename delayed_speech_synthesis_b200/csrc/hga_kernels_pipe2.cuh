@@ -29,35 +29,6 @@
 
 namespace hga {
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
-// Table-driven natural log for finite x > 0: x = m * 2^e, m in [1, 2); the top 7 mantissa bits pick c = 1 + (i + 1/2) / 128,
-// log m = -log(1/c) + log1p(r) with r = m * (1/c) - 1 (one FMA, |r| <= 2^-8) and a degree-6 series (truncation < 2e-18).
-// The table holds the ROUNDED 1/c and -log of that rounded value (computed in long double on the host, hga_api.cu), so
-// the split is exact.  ~10 FP64 instructions against ~45 for fast_log: on the float64 path, where the FP64 pipe is the
-// binding unit, the log costs 1.0 instead of 4.5 pipe slots per channel-sample-hop.  |error| <= 3e-16 over [1e-2, 1e15]
-// (tools/check_fast_log.py).
-constexpr int kLogTabN = 128;
-__device__ double g_logtab[2 * kLogTabN];
-__device__ __forceinline__ double tab_log(double x, const double* __restrict__ tab) {
-  const long long bits = __double_as_longlong(x);
-  const int hi = (int)(bits >> 32);
-  const int e = ((hi >> 20) & 0x7ff) - 1023;
-  const int idx = (hi >> 13) & (kLogTabN - 1);
-  const double m = __longlong_as_double((bits & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);
-  const double2 t = *reinterpret_cast<const double2*>(tab + 2 * idx);
-  const double r = fma(m, t.x, -1.0);
-  double qv = fma(r, -1.0 / 6.0, 1.0 / 5.0);
-  qv = fma(r, qv, -1.0 / 4.0);
-  qv = fma(r, qv, 1.0 / 3.0);
-  qv = fma(r, qv, -0.5);
-  const double ed = (double)e;
-  const double lo = fma(r * r, qv, r);
-  return fma(ed, 0x1.62e42fee00000p-1, t.y) + fma(ed, 0x1.a39ef35793c76p-33, lo);
-}
-
 template <int S, int TB, typename T>
 struct Pipe2Smem {
   static constexpr int CPL = PipeTraits<T>::CPL;
