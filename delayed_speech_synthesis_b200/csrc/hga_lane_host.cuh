@@ -138,8 +138,9 @@ inline double lane_transition(const LaneConst& k, int64_t n, double* M) {
   return mx;
 }
 
-// Pieces of the head fix-up (k_lane_fix_sums) and their start-state operators: the staged zero-input evolution of the 32
-// unit states, sampled where a piece starts.  Pieces are cut to roughly equal operation counts so that they finish together.
+// Pieces of the head fix-up (k_lane_fix) and their start-state operators: the staged zero-input evolution of the 32 unit
+// states, sampled where a piece starts.  Pieces are cut to roughly equal operation counts so that they finish together;
+// every piece but the first starts kLaneNB - 1 hop blocks before the first frame it finishes.
 struct LaneFixPlan {
   std::vector<LaneSub> subs;
   std::vector<double> P;
@@ -147,41 +148,41 @@ struct LaneFixPlan {
 inline void lane_build_fix(const LaneConst& k, int hop, LaneFixPlan& fp, double piece_ops = 14000.0) {
   constexpr int N = kLaneState;
   const int first[kLaneStages] = {0, 8, 10, 12, 14};
+  const int K = lane_carry_rows(k);
+  const int head_blocks = K / hop + (kLaneNB - 1);
+  auto stage_of = [&](int row) {
+    int st = 0;
+    while (st + 1 < kLaneStages && row >= k.stage_rows[st]) ++st;
+    return st;
+  };
   fp.subs.clear();
   fp.P.clear();
-  std::vector<char> start(lane_carry_rows(k) + 1, 0);
-  for (int i = 0, r0 = 0; i < kLaneStages; ++i) {
-    const int r1 = k.stage_rows[i];
-    if (r1 > r0) {
-      int ops = 0;
-      for (int s = first[i]; s < 16; ++s) ops += s < 8 ? 3 : 4;
-      const int n = std::max(1, (int)std::ceil((double)(r1 - r0) * ops / piece_ops));
-      const int len = ((r1 - r0 + n - 1) / n + hop - 1) / hop * hop;
-      for (int r = r0; r < r1; r += len) {
-        fp.subs.push_back(LaneSub{r, std::min(len, r1 - r), first[i], 0});
-        start[r] = 1;
-      }
-    }
-    r0 = r1;
+  std::vector<char> start((size_t)K + 1, 0);
+  for (int b0 = 0; b0 < head_blocks;) {
+    const int row0 = std::max(0, b0 - (kLaneNB - 1)) * hop;
+    const int f = first[stage_of(std::min(row0, K - 1))];
+    int ops = 1;   // the square and the add of every row
+    for (int s = f; s < 16; ++s) ops += s < 8 ? 3 : 4;
+    int nb = std::max(2 * kLaneNB, (int)std::ceil(piece_ops / ((double)ops * hop)));
+    if (head_blocks - (b0 + nb) < kLaneNB) nb = head_blocks - b0;   // no sliver at the end
+    fp.subs.push_back(LaneSub{row0, b0, b0 + nb, f, 0, 0});
+    if (row0 < K) start[row0] = 1;
+    b0 += nb;
   }
   // evolve the 32 unit states (columns of S) and sample
   std::vector<double> S(N * N, 0.0);
   for (int i = 0; i < N; ++i) S[i * N + i] = 1.0;
-  size_t at = 0;
-  int stage = 0;
-  const int K = lane_carry_rows(k);
   for (int r = 0; r < K; ++r) {
-    while (stage + 1 < kLaneStages && r >= k.stage_rows[stage]) ++stage;
-    const int f = first[stage];
-    if (start[r]) {
-      while (at < fp.subs.size() && fp.subs[at].row0 != r) ++at;
-      if (r > 0) {
-        fp.subs[at].p_off = (int32_t)fp.P.size();
-        for (int s = f; s < 16; ++s)
-          for (int j = 0; j < N; ++j) fp.P.push_back(S[s * N + j]);
-        for (int s = f; s < 16; ++s)
-          for (int j = 0; j < N; ++j) fp.P.push_back(S[(16 + s) * N + j]);
-      }
+    const int f = first[stage_of(r)];
+    if (start[r] && r > 0) {
+      for (LaneSub& sub : fp.subs)
+        if (sub.row0 == r) {
+          sub.p_off = (int32_t)fp.P.size();
+          for (int s = f; s < 16; ++s)
+            for (int j = 0; j < N; ++j) fp.P.push_back(S[s * N + j]);
+          for (int s = f; s < 16; ++s)
+            for (int j = 0; j < N; ++j) fp.P.push_back(S[(16 + s) * N + j]);
+        }
     }
     for (int j = 0; j < N; ++j) {  // one zero-input step of sections [f, 16) on column j; the dropped sections are at rest
       double u = 0.0;
@@ -202,7 +203,6 @@ inline void lane_build_fix(const LaneConst& k, int hop, LaneFixPlan& fp, double 
       }
     }
   }
-  fp.subs.push_back(LaneSub{K, (kLaneNB - 1) * hop, 16, 0});  // behind the reach of the carry: block sums only
   if (fp.P.empty()) fp.P.push_back(0.0);
 }
 
@@ -313,7 +313,7 @@ inline void lane_plan(const LaneConst& k, int hop, int C, int cw, int n_seg, con
         f.head_off = p.y_rows;
         f.bs_off = p.bs_rows;
         p.y_rows += f.head_rows;
-        p.bs_rows += (kLaneNB - 1) + f.head_rows / hop;
+        p.bs_rows += 2 * (kLaneNB - 1);   // the predecessor's last four block sums and this head's first four
         p.max_fix_frames = std::max(p.max_fix_frames, f.n_frames);
         w.head_off = f.head_off;
         w.head_rows = f.head_rows;
@@ -373,22 +373,8 @@ inline CUresult lane_tensor_map(LaneEncodeFn enc, const double* x_base, int64_t 
              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
 
-// The launch sequence of one extraction: item counter reset, k_hga_lane, then (if any chunk has a predecessor) the state
-// carry, the head fix-up and the frames touching the heads.  Returns the number of kernels launched, or -1 on a CUDA error.
-template <class P, int HOP, int TB, int NW, int NSLOT, int U, bool PROF = false>
-inline int lane_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma,
-                         double* out, int64_t ldo, int n_sm, cudaStream_t st, long long* prof = nullptr) {
-  using SM = LaneSmem<32 * P::CPL, TB, NW, NSLOT>;
-  auto kern = k_hga_lane<P, HOP, TB, NW, NSLOT, U, PROF>;
-  static_assert(32 * P::CPL > 0, "");
-  static bool attr_set[64] = {};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::total) != cudaSuccess) return -1;
-    attr_set[dev & 63] = true;
-  }
-  LaneArgs a{};
+inline void lane_fill_args(const LanePlan& p, const LaneDev& d, int C, const double* mu, const double* sigma, double* out, int64_t ldo, long long* prof, LaneArgs& a) {
+  a = LaneArgs{};
   a.work = d.work;
   a.n_work = (int)p.work.size();
   a.groups = p.groups;
@@ -405,26 +391,72 @@ inline int lane_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d
   a.counter = d.counter;
   a.order = d.order;
   a.prof = prof;
+}
+// State carry, head fix-up and the frames touching the heads (after the main kernel, same stream).  Returns the number of
+// kernels launched.
+template <typename TY, int HOP>
+inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev& d, int C, const double* mu, const double* sigma, double* out, int64_t ldo,
+                           cudaStream_t st) {
+  const int n_fix = (int)p.fix.size();
+  if (n_fix == 0) return 0;
+  const int CP = p.groups * p.cw;
+  int launches = 0;
+  const double* s0 = d.E;
+  if (d.M) {
+    const int warps = (int)p.segs.size() * C;
+    k_lane_carry<<<(warps + 3) / 4, 128, 0, st>>>(d.E, d.S0, d.M, d.segs, (int)p.segs.size(), C, CP);
+    s0 = d.S0;
+    ++launches;
+  }
+  constexpr int CPT = LaneFixOf<TY>::type::CPT;
+  const dim3 g1((unsigned)(n_fix * d.n_sub), (unsigned)((CP / CPT + 63) / 64));
+  k_lane_fix<TY, HOP><<<g1, 64, 0, st>>>(k, d.fix, d.subs, d.n_sub, d.P, C, CP, d.ybuf, s0, d.bs, mu, sigma, out, ldo);
+  const dim3 g2((unsigned)n_fix, (unsigned)((C + 127) / 128));
+  k_lane_fix_frames<<<g2, 128, 0, st>>>(k, d.fix, n_fix, C, CP, d.bs, mu, sigma, out, ldo);
+  return launches + 2;
+}
+template <class KernT>
+inline bool lane_set_smem(KernT kern, size_t bytes, bool (&done)[64]) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!done[dev & 63]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) return false;
+    done[dev & 63] = true;
+  }
+  return true;
+}
+
+// The launch sequence of one extraction with the one-warp-per-item kernel: item counter reset, k_hga_lane, then (if any
+// chunk has a predecessor) the fix-up kernels.  Returns the number of kernels launched, or -1 on a CUDA error.
+template <class P, int HOP, int TB, int NW, int NSLOT, int U, bool PROF = false>
+inline int lane_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma,
+                         double* out, int64_t ldo, int n_sm, cudaStream_t st, long long* prof = nullptr) {
+  using SM = LaneSmem<32 * P::CPL, TB, NW, NSLOT>;
+  auto kern = k_hga_lane<P, HOP, TB, NW, NSLOT, U, PROF>;
+  static bool attr_set[64] = {};
+  if (!lane_set_smem(kern, SM::total, attr_set)) return -1;
+  LaneArgs a;
+  lane_fill_args(p, d, C, mu, sigma, out, ldo, prof, a);
   if (cudaMemsetAsync(d.counter, 0, sizeof(int), st) != cudaSuccess) return -1;
   const int grid = std::max(1, std::min(n_sm, (a.n_items + NW - 1) / NW));
   kern<<<grid, 32 * NW, SM::total, st>>>(k, a, tm);
-  int launches = 1;
-  const int n_fix = (int)p.fix.size();
-  if (n_fix > 0) {
-    const double* s0 = d.E;
-    if (d.M) {
-      const int warps = (int)p.segs.size() * C;
-      k_lane_carry<<<(warps + 3) / 4, 128, 0, st>>>(d.E, d.S0, d.M, d.segs, (int)p.segs.size(), C, a.CP);
-      s0 = d.S0;
-      ++launches;
-    }
-    const int g32 = a.CP / 32;  // the fix-up kernels work on 32-channel groups whatever the main kernel's group width
-    const dim3 g1((unsigned)(n_fix * d.n_sub), (unsigned)((g32 + 3) / 4));
-    k_lane_fix_sums<typename P::TY, HOP><<<g1, 128, 0, st>>>(k, d.fix, d.subs, d.n_sub, d.P, g32, a.CP, d.ybuf, s0, d.bs);
-    const dim3 g2((unsigned)(n_fix * g32), (unsigned)((p.max_fix_frames + 4 * kLaneFrameRun - 1) / (4 * kLaneFrameRun)));
-    k_lane_fix_frames<<<g2, 128, 0, st>>>(k, d.fix, g32, C, a.CP, d.bs, mu, sigma, out, ldo);
-    launches += 2;
-  }
+  const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
+  return cudaGetLastError() == cudaSuccess ? launches : -1;
+}
+// The same with the section-pipelined kernel (NS warps per item, NI items per CTA).
+template <class P, int HOP, int TB, int NI, int NS, int NSLOT, int NL, int U, bool PROF = false>
+inline int lanes_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma,
+                          double* out, int64_t ldo, int n_sm, cudaStream_t st, long long* prof = nullptr) {
+  using SM = LanesSmem<32 * P::CPL, TB, NI, NS, NSLOT, NL>;
+  static_assert(SM::total <= 232448, "more than 227 KB of shared memory");
+  auto kern = k_hga_lanes<P, HOP, TB, NI, NS, NSLOT, NL, U, PROF>;
+  static bool attr_set[64] = {};
+  if (!lane_set_smem(kern, SM::total, attr_set)) return -1;
+  LaneArgs a;
+  lane_fill_args(p, d, C, mu, sigma, out, ldo, prof, a);
+  const int grid = std::max(1, std::min(n_sm, (a.n_items + NI - 1) / NI));
+  kern<<<grid, 32 * NI * NS, SM::total, st>>>(k, a, tm);
+  const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
   return cudaGetLastError() == cudaSuccess ? launches : -1;
 }
 

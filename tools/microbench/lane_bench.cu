@@ -134,7 +134,7 @@ struct DevPlan {
   }
 };
 
-static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, size_t ysize, DevPlan& dp, bool verbose) {
+static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, size_t ysize, DevPlan& dp, bool verbose, double tol = 1e-11) {
   dp.d.work = dp.up(p.work);
   dp.d.fix = dp.up(p.fix);
   dp.d.segs = dp.up(p.segs);
@@ -152,15 +152,36 @@ static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, s
   dp.d.P = dp.up(fp.P);
   std::vector<double> M(kLaneState * kLaneState);
   const double mx = lane_transition(k, p.Lc, M.data());
-  dp.d.M = mx > 1e-18 ? dp.up(M) : nullptr;
+  dp.d.M = mx > 1e-3 * tol ? dp.up(M) : nullptr;   // the carry is only propagated across a chunk when it survives it
   if (verbose)
     printf("  plan: Lc=%lld chunks=%zu fixups=%zu head rows=%lld (%.1f MB) carry rows=%d pieces=%d |A^Lc|max=%.2e%s\n", (long long)p.Lc, p.work.size(),
            p.fix.size(), (long long)p.y_rows, (double)p.y_rows * CP * ysize / 1e6, lane_carry_rows(k), dp.d.n_sub, mx, dp.d.M ? "" : " (underflows: no propagation)");
 }
 
 template <class P, int HOP, int TB, int NW, int NSLOT, int U>
+struct OneStage {
+  using Pol = P;
+  static constexpr int hop = HOP, tb = TB, workers_per_sm = NW, prof_warps = NW;
+  template <bool PROF>
+  static int launch(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma, double* out, int n_sm, long long* prof) {
+    return lane_launch_t<P, HOP, TB, NW, NSLOT, U, PROF>(k, p, d, tm, C, mu, sigma, out, C, n_sm, 0, prof);
+  }
+};
+template <class P, int HOP, int TB, int NI, int NS, int NSLOT, int NL, int U>
+struct Staged {
+  using Pol = P;
+  static constexpr int hop = HOP, tb = TB, workers_per_sm = NI, prof_warps = NI * NS;
+  template <bool PROF>
+  static int launch(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma, double* out, int n_sm, long long* prof) {
+    return lanes_launch_t<P, HOP, TB, NI, NS, NSLOT, NL, U, PROF>(k, p, d, tm, C, mu, sigma, out, C, n_sm, 0, prof);
+  }
+};
+
+template <class V>
 static float run_variant(const char* name, const LaneConst& k, const LanePlan& p, const DevPlan& dp, const double* x, int64_t ldx, int64_t T, int C, const double* mu,
                          const double* sigma, double* out, int n_sm, int reps, bool prof) {
+  using P = typename V::Pol;
+  constexpr int HOP = V::hop, TB = V::tb, NW = V::prof_warps;
   CUtensorMap tm;
   if (lane_tensor_map(encode_fn(), x, ldx, C, T, 32 * P::CPL, TB, &tm) != CUDA_SUCCESS) { fprintf(stderr, "tensor map failed\n"); exit(2); }
   cudaEvent_t e0, e1;
@@ -170,13 +191,13 @@ static float run_variant(const char* name, const LaneConst& k, const LanePlan& p
   const size_t nprof = (size_t)n_sm * NW * 3;
   if (prof) { CK(cudaMalloc(&dprof, nprof * 8)); CK(cudaMemset(dprof, 0, nprof * 8)); }
   for (int i = 0; i < 2; ++i)
-    if ((prof ? lane_launch_t<P, HOP, TB, NW, NSLOT, U, true>(k, p, dp.d, tm, C, mu, sigma, out, C, n_sm, 0, dprof)
-              : lane_launch_t<P, HOP, TB, NW, NSLOT, U>(k, p, dp.d, tm, C, mu, sigma, out, C, n_sm, 0, nullptr)) < 0) { fprintf(stderr, "%s: launch failed: %s\n", name, cudaGetErrorString(cudaGetLastError())); exit(2); }
+    if ((prof ? V::template launch<true>(k, p, dp.d, tm, C, mu, sigma, out, n_sm, dprof)
+              : V::template launch<false>(k, p, dp.d, tm, C, mu, sigma, out, n_sm, nullptr)) < 0) { fprintf(stderr, "%s: launch failed: %s\n", name, cudaGetErrorString(cudaGetLastError())); exit(2); }
   CK(cudaDeviceSynchronize());
   float best = 1e30f, sum = 0.f;
   for (int i = 0; i < reps; ++i) {
     CK(cudaEventRecord(e0));
-    lane_launch_t<P, HOP, TB, NW, NSLOT, U>(k, p, dp.d, tm, C, mu, sigma, out, C, n_sm, 0, nullptr);
+    V::template launch<false>(k, p, dp.d, tm, C, mu, sigma, out, n_sm, nullptr);
     CK(cudaEventRecord(e1));
     CK(cudaEventSynchronize(e1));
     float ms;
@@ -203,25 +224,27 @@ static float run_variant(const char* name, const LaneConst& k, const LanePlan& p
   return sum / reps;
 }
 
-template <class P, int HOP, int TB, int NW, int NSLOT, int U>
+template <class V>
 static double check_variant(const char* name, const Coefs& co, int fs, int64_t T, int C, int64_t force_Lc, double tol_carry, const std::vector<double>& ref,
                             const double* x, const double* mu, const double* sigma, int n_sm) {
+  using P = typename V::Pol;
+  constexpr int HOP = V::hop, TB = V::tb;
   Cascade q;
   build_cascade(co, q);
   LaneConst k;
   lane_build_const(q, 5 * HOP, HOP, 0.01, tol_carry, k);
   LanePlan p;
   const int64_t s0 = 0, o0 = 0;
-  lane_plan(k, HOP, C, 32 * P::CPL, 1, &s0, &T, &o0, 0, (int64_t)n_sm * NW, true, p, force_Lc);
+  lane_plan(k, HOP, C, 32 * P::CPL, 1, &s0, &T, &o0, 0, (int64_t)n_sm * V::workers_per_sm, true, p, force_Lc);
   DevPlan dp;
-  upload_plan(k, p, C, HOP, sizeof(typename P::TY), dp, true);
+  upload_plan(k, p, C, HOP, sizeof(typename P::TY), dp, true, tol_carry);
   const int64_t F = (T - 5 * HOP) / HOP + 1;
   double* out;
   CK(cudaMalloc(&out, (size_t)F * C * 8));
   CK(cudaMemset(out, 0xff, (size_t)F * C * 8));  // NaN pattern: every frame must be written
   CUtensorMap tm;
   lane_tensor_map(encode_fn(), x, C, C, T, 32 * P::CPL, TB, &tm);
-  if (lane_launch_t<P, HOP, TB, NW, NSLOT, U>(k, p, dp.d, tm, C, mu, sigma, out, C, n_sm, 0, nullptr) < 0) { fprintf(stderr, "launch failed\n"); exit(2); }
+  if (V::template launch<false>(k, p, dp.d, tm, C, mu, sigma, out, n_sm, nullptr) < 0) { fprintf(stderr, "launch failed\n"); exit(2); }
   CK(cudaDeviceSynchronize());
   std::vector<double> got((size_t)F * C);
   CK(cudaMemcpy(got.data(), out, got.size() * 8, cudaMemcpyDeviceToHost));
@@ -275,18 +298,23 @@ int main(int argc, char** argv) {
       auto expect = [&](double err, double tol) { if (!(err <= tol)) { ++fails; printf("   ^^^ FAIL (tolerance %.1e)\n", tol); } };
       if (fs == 1000) {
         for (int64_t Lc : {(int64_t)0, (int64_t)1 << 30, (int64_t)30000, (int64_t)2500, (int64_t)400}) {  // planner, one chunk, long, shorter than the carry, tiny
-          expect(check_variant<LaneF64, 10, 80, 4, 2, 5>("f64 TB80 NW4 NS2 U5", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
-          expect(check_variant<LaneF32, 10, 50, 4, 2, 5>("f32 TB50 NW4 NS2 U5", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
-          expect(check_variant<LaneMix, 10, 50, 4, 2, 5>("mix TB50 NW4 NS2 U5", co, fs, T, C, Lc, 1e-7, ref, x, dmu, dsig, n_sm), 5e-3);
+          expect(check_variant<OneStage<LaneF64, 10, 80, 4, 2, 5>>("f64 TB80 NW4 NS2 U5", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
+          expect(check_variant<OneStage<LaneF32, 10, 50, 4, 2, 5>>("f32 TB50 NW4 NS2 U5", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
+          expect(check_variant<OneStage<LaneMix, 10, 50, 4, 2, 5>>("mix TB50 NW4 NS2 U5", co, fs, T, C, Lc, 1e-7, ref, x, dmu, dsig, n_sm), 5e-3);
+          expect(check_variant<Staged<LaneF32, 10, 50, 2, 2, 2, 3, 5>>("f32 2-stage x2 TB50", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
+          expect(check_variant<Staged<LaneF32, 10, 40, 2, 4, 2, 2, 5>>("f32 4-stage x2 TB40", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
+          expect(check_variant<Staged<LaneF64, 10, 50, 2, 4, 2, 2, 5>>("f64 4-stage x2 TB50", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
         }
-        expect(check_variant<LaneF64, 10, 40, 8, 2, 5>("f64 TB40 NW8 NS2 U5", co, fs, T, C, 0, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
-        expect(check_variant<LaneF32, 10, 30, 4, 3, 5>("f32 TB30 NW4 NS3 U5", co, fs, T, C, 5000, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
-        expect(check_variant<LaneF32, 10, 20, 8, 2, 5>("f32 TB20 NW8 NS2 U5", co, fs, T, C, 5000, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
+        expect(check_variant<OneStage<LaneF64, 10, 40, 8, 2, 5>>("f64 TB40 NW8 NS2 U5", co, fs, T, C, 0, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
+        expect(check_variant<OneStage<LaneF32, 10, 30, 4, 3, 5>>("f32 TB30 NW4 NS3 U5", co, fs, T, C, 5000, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
+        expect(check_variant<OneStage<LaneF32, 10, 20, 8, 2, 5>>("f32 TB20 NW8 NS2 U5", co, fs, T, C, 5000, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
       } else {
         for (int64_t Lc : {(int64_t)0, (int64_t)40000, (int64_t)3000}) {
-          expect(check_variant<LaneF64, 20, 80, 4, 2, 5>("f64 hop20 TB80 NW4 NS2 U5", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
-          expect(check_variant<LaneF32, 20, 40, 4, 2, 5>("f32 hop20 TB40 NW4 NS2 U5", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 2e-2);
-          expect(check_variant<LaneMix, 20, 40, 4, 2, 10>("mix hop20 TB40 NW4 NS2 U10", co, fs, T, C, Lc, 1e-7, ref, x, dmu, dsig, n_sm), 2e-2);
+          expect(check_variant<OneStage<LaneF64, 20, 80, 4, 2, 5>>("f64 hop20 TB80 NW4 NS2 U5", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
+          expect(check_variant<OneStage<LaneF32, 20, 40, 4, 2, 5>>("f32 hop20 TB40 NW4 NS2 U5", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 2e-2);
+          expect(check_variant<Staged<LaneF32, 20, 40, 2, 4, 2, 2, 5>>("f32 4-stage x2 hop20 TB40", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 2e-2);
+          expect(check_variant<Staged<LaneF64, 20, 40, 2, 4, 2, 2, 10>>("f64 4-stage x2 hop20 TB40 U10", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
+          expect(check_variant<OneStage<LaneMix, 20, 40, 4, 2, 10>>("mix hop20 TB40 NW4 NS2 U10", co, fs, T, C, Lc, 1e-7, ref, x, dmu, dsig, n_sm), 2e-2);
         }
       }
       cudaFree(x); cudaFree(dmu); cudaFree(dsig);
@@ -305,21 +333,28 @@ int main(int argc, char** argv) {
       CK(cudaDeviceSynchronize());
       const int reps = T >= 3000000 ? 10 : 20;
       printf("== timing, T = %lld rows x %d channels\n", (long long)T, C);
-#define TIME_V(P, TOL, TB, NW, NS, U, NAME)                                                          \
+#define TIME_X(V, TOL, NAME)                                                                         \
   {                                                                                                  \
     LaneConst k;                                                                                     \
     lane_build_const(q, 5 * hop, hop, 0.01, TOL, k);                                                 \
     LanePlan p;                                                                                      \
     const int64_t s0 = 0, o0 = 0;                                                                    \
-    lane_plan(k, hop, C, 32 * P::CPL, 1, &s0, &T, &o0, 0, (int64_t)n_sm * NW, true, p, 0);                        \
+    lane_plan(k, hop, C, 32 * V::Pol::CPL, 1, &s0, &T, &o0, 0, (int64_t)n_sm * V::workers_per_sm, true, p, 0); \
     DevPlan dp;                                                                                      \
-    upload_plan(k, p, C, hop, sizeof(typename P::TY), dp, true);                                     \
-    run_variant<P, 10, TB, NW, NS, U>(NAME, k, p, dp, x, C, T, C, nullptr, nullptr, out, n_sm, reps, true); \
+    upload_plan(k, p, C, hop, sizeof(typename V::Pol::TY), dp, true, TOL);                           \
+    run_variant<V>(NAME, k, p, dp, x, C, T, C, nullptr, nullptr, out, n_sm, reps, true);             \
     dp.release();                                                                                    \
   }
+#define SINGLE_ARG(...) __VA_ARGS__
+#define TIME_V(P, TOL, TB, NW, NS, U, NAME) { using V_ = OneStage<P, 10, TB, NW, NS, U>; TIME_X(V_, TOL, NAME) }
+#define TIME_S(P, TOL, TB, NI, NST, NS, NL, U, NAME) { using V_ = Staged<P, 10, TB, NI, NST, NS, NL, U>; TIME_X(V_, TOL, NAME) }
+      TIME_S(LaneF32, 1e-6, 40, 2, 4, 2, 2, 5, "f32 4-stage x2 TB40 NS2 NL2")
+      TIME_S(LaneF32, 1e-6, 30, 2, 4, 2, 3, 5, "f32 4-stage x2 TB30 NS2 NL3")
+      TIME_S(LaneF32, 1e-6, 60, 2, 2, 2, 3, 5, "f32 2-stage x2 TB60")
+      TIME_S(LaneF32, 1e-6, 30, 4, 2, 2, 2, 5, "f32 2-stage x4 TB30")
+      TIME_S(LaneF64, 1e-11, 50, 2, 4, 2, 2, 5, "f64 4-stage x2 TB50 NS2 NL2")
+      TIME_S(LaneF64, 1e-11, 80, 2, 2, 2, 3, 5, "f64 2-stage x2 TB80")
       TIME_V(LaneF32, 1e-6, 50, 4, 2, 5, "f32 TB50 NW4 NS2 U5")
-      TIME_V(LaneF32, 1e-6, 30, 4, 3, 5, "f32 TB30 NW4 NS3 U5")
-      TIME_V(LaneF32, 1e-6, 20, 8, 2, 5, "f32 TB20 NW8 NS2 U5")
       TIME_V(LaneMix, 1e-7, 50, 4, 2, 5, "mix TB50 NW4 NS2 U5")
       TIME_V(LaneF64, 1e-11, 80, 4, 2, 5, "f64 TB80 NW4 NS2 U5")
       TIME_V(LaneF64, 1e-11, 100, 4, 2, 5, "f64 TB100 NW4 NS2 U5")
@@ -340,9 +375,9 @@ int main(int argc, char** argv) {
     CK(cudaDeviceSynchronize());
     const int reps = 2;
     const std::string which = argc > 3 ? argv[3] : "f32";
-    if (which == "f32") TIME_V(LaneF32, 1e-6, 50, 4, 2, 5, "f32 TB50 NW4 NS2 U5")
+    if (which == "f32") TIME_S(LaneF32, 1e-6, 40, 2, 4, 2, 2, 5, "f32 4-stage x2 TB40 NS2 NL2")
     else if (which == "mix") TIME_V(LaneMix, 1e-7, 50, 4, 2, 5, "mix TB50 NW4 NS2 U5")
-    else TIME_V(LaneF64, 1e-11, 80, 4, 2, 5, "f64 TB80 NW4 NS2 U5")
+    else TIME_S(LaneF64, 1e-11, 50, 2, 4, 2, 2, 5, "f64 4-stage x2 TB50 NS2 NL2")
   }
   printf(fails ? "RESULT: %d parity failures\n" : "RESULT: parity ok\n", fails);
   return fails ? 1 : 0;
