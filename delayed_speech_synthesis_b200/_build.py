@@ -39,7 +39,9 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         raise RuntimeError("nvcc not found: cannot build libhga_b200.so")
     cmd = [nvcc, *NVCC_FLAGS, "-o", str(LIB), *map(str, SOURCES)]
     res = subprocess.run(cmd, capture_output=True, text=True)
-    (PKG / "csrc" / "ptxas.log").write_text(res.stdout + res.stderr)
+    log = PKG.parent / "gpurun_out"   # scratch, git-ignored: register / spill report of the last build
+    log.mkdir(exist_ok=True)
+    (log / "ptxas.log").write_text(res.stdout + res.stderr)
     if res.returncode != 0:
         raise RuntimeError(f"nvcc failed:\n{res.stdout}\n{res.stderr}")
     if verbose:

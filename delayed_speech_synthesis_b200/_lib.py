@@ -9,8 +9,8 @@ from . import _build
 
 HGA_ABI_VERSION = 1
 HGA_MAX_SECTIONS = 8
-PREC_EXACT, PREC_F64, PREC_F32 = 0, 1, 2
-PRECISIONS = {"exact": PREC_EXACT, "f64": PREC_F64, "f32": PREC_F32}
+PREC_EXACT, PREC_F64, PREC_F32, PREC_MIXED = 0, 1, 2, 3
+PRECISIONS = {"exact": PREC_EXACT, "f64": PREC_F64, "f32": PREC_F32, "mixed": PREC_MIXED}
 
 
 class HgaError(RuntimeError):
@@ -43,6 +43,7 @@ SIGNATURES = {
     "hga_destroy": (C.c_int, [_vp]),
     "hga_reset": (C.c_int, [_vp, _vp]),
     "hga_warmup": (C.c_int, [_vp]),
+    "hga_last_plan": (C.c_int, [_vp, _pi64, _pi32, _pi32, _pi32]),
     "hga_num_frames": (_i64, [_vp, _i64]),
     "hga_extract_offline": (C.c_int, [_vp, _vp, _i64, _i32, _pi64, _pi64, _pi64, _vp, _vp, _vp, _i64, _vp]),
     "hga_extract_offline_host": (C.c_int, [_vp, _vp, _i64, _i32, _pi64, _pi64, _pi64, _vp, _vp, _vp, _i64]),
@@ -57,6 +58,7 @@ SIGNATURES = {
     "hga_stats_accumulate": (C.c_int, [_i32, _vp, _i64, _i32, _i64, _vp, _vp]),
     "hga_stats_merge": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _vp]),
     "hga_stats_finalize": (C.c_int, [_i32, _vp, _i32, _vp, _vp, _vp]),
+    "hga_stats_merge_days": (C.c_int, [_i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
     "hga_chanmap_create": (C.c_int, [_i32, _i32, _i32, _pi32, _pi32, _vp, _vp, _i32, _pi32, _pi32, C.POINTER(_vp)]),
     "hga_chanmap_destroy": (C.c_int, [_vp]),
     "hga_chanmap_apply": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64, _vp]),

@@ -34,6 +34,106 @@ def day_slots(days: Sequence[int]) -> Dict[int, int]:
     return {d: i for i, d in enumerate(sorted(set(days)))}
 
 
+def merge_days(gathered, n_src: int, n_days: int):
+    """(n_src, n_days, 3, C) gathered accumulators -> (mu, sigma), each (n_days, C): per (day, channel) a fixed-order Chan
+    merge over the sources, then mu = mean, sigma = sqrt(M2 / n).  One kernel launch on CUDA tensors
+    (`hga_stats_merge_days`); CPU tensors (gloo host-logic tests) take the same arithmetic in torch."""
+    import torch
+
+    g = gathered.reshape(n_src, n_days, 3, gathered.shape[-1])
+    Cn = g.shape[-1]
+    if g.is_cuda:
+        from . import _lib
+        from .engine import _stream_ptr
+
+        g = g.contiguous()
+        mu = torch.empty((n_days, Cn), dtype=torch.float64, device=g.device)
+        sigma = torch.empty_like(mu)
+        dev = g.device.index if g.device.index is not None else torch.cuda.current_device()
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().hga_stats_merge_days(dev, g.data_ptr(), n_src, n_days, Cn, mu.data_ptr(), sigma.data_ptr(), _stream_ptr(dev)))
+        return mu, sigma
+    n = torch.zeros((n_days, Cn), dtype=torch.float64)
+    mean = torch.zeros_like(n)
+    m2 = torch.zeros_like(n)
+    for r in range(n_src):                                    # the kernel's chan_merge, source by source
+        bn, bmean, bm2 = g[r, :, 0], g[r, :, 1], g[r, :, 2]
+        tot = n + bn
+        w = torch.where(tot > 0, bn / torch.where(tot > 0, tot, torch.ones_like(tot)), torch.zeros_like(tot))
+        d = bmean - mean
+        keep = tot > 0
+        mean = torch.where(keep, mean + d * w, mean)
+        m2 = torch.where(keep, m2 + bm2 + d * d * n * w, m2)
+        n = torch.where(keep, tot, n)
+    has = n > 0
+    safe = torch.where(has, n, torch.ones_like(n))
+    return torch.where(has, mean, torch.zeros_like(mean)), torch.where(has, torch.sqrt(m2 / safe), torch.ones_like(m2))
+
+
+def _chan_merge(a, b):
+    """(3, C) accumulators (n, mean, M2): Chan et al.'s pairwise merge, elementwise on the tensors' device."""
+    import torch
+
+    n = a[0] + b[0]
+    safe = torch.where(n > 0, n, torch.ones_like(n))
+    w, d = b[0] / safe, b[1] - a[1]
+    return torch.stack([n, a[1] + d * w, a[2] + b[2] + d * d * a[0] * w])
+
+
+def extract_corpus(n_sessions: int, day_of, baseline_sessions, get_session, extract, accumulate, *, n_channels: int, device=None,
+                   group=None, on_features=None, timings: Optional[dict] = None):
+    """The reference's corpus build (prepare_corpus.py:179-236) over the ranks of a process group, one process per GPU:
+
+      1. `ZScoresFromSyllableRepetitions` (:183-199): per day, (n, mean, M2) of the features of that day's baseline
+         session(s); every rank does this for the baseline sessions it owns (sessions are dealt round-robin,
+         `shard_sessions`), days it owns nothing of stay (0, 0, 0);
+      2. ONE exchange: all days' accumulators in one all-gather (3 * C float64 per day and rank; NCCL over NVLink on CUDA
+         tensors), then the same fixed-order merge on every rank (`merge_days`) -> bit-identical (mu, sigma) everywhere;
+      3. the main loop (:209-234): every owned session extracted and z-scored with its day's (mu, sigma) (:226-227).
+
+    day_of[s]: day label of session s.  baseline_sessions: session ids whose features define their day's statistics.
+    get_session(s) -> the session's recording (device tensor).  extract(x, mu, sigma) -> (F, C) features (mu = None: raw
+    log-power).  accumulate(features) -> (3, C) tensor (n, mean, M2).  on_features(s, features): what the caller does with
+    a finished session (the reference writes an HDF5 file, :233-234).  timings: optional dict that receives CUDA events
+    bracketing the exchange (`exchange_events`) when the tensors live on a device.
+    Returns (mu, sigma, slots): (n_days, C) tensors and the day -> row table."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    slots = day_slots([day_of[s] for s in range(n_sessions)])
+    n_days = len(slots)
+    mine = shard_sessions(n_sessions, rank, world)
+    base = set(int(b) for b in baseline_sessions)
+    acc = None
+    for s in mine:
+        if s in base:
+            a = accumulate(extract(get_session(s), None, None))
+            if acc is None:
+                acc = torch.zeros((n_days, 3, n_channels), dtype=torch.float64, device=a.device)
+            d = slots[day_of[s]]
+            acc[d] = _chan_merge(acc[d], a)          # several baseline sessions of one day on this rank: in session order
+    if acc is None:
+        dev = torch.device("cuda", device) if device is not None else torch.device("cpu")
+        acc = torch.zeros((n_days, 3, n_channels), dtype=torch.float64, device=dev)
+    ev = None
+    if acc.is_cuda and timings is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record()
+    gathered = gather_accumulators(acc, group)                      # (world * n_days, 3, C), rank-major
+    mu, sigma = merge_days(gathered, world, n_days)
+    if ev is not None:
+        ev[1].record()
+        timings.setdefault("exchange_events", []).append(ev)
+    for s in mine:
+        d = slots[day_of[s]]
+        f = extract(get_session(s), mu[d], sigma[d])
+        if on_features is not None:
+            on_features(s, f)
+    return mu, sigma, slots
+
+
 # ---------------------------------------------------------------------------------------------- per-trial extraction
 def trial_segments(trial_indices, fs: float, n_rows: int, tail: float = 0.04):
     """The row ranges `FeatureExtractionPipeline.get_features` slices out of a recording (prepare_corpus.py:47-50):

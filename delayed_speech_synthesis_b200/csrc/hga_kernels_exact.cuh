@@ -17,13 +17,16 @@ template <int ARITH>
 __global__ void __launch_bounds__(128) k_iir_seq(const __grid_constant__ Cascade q, const double* __restrict__ x,
                                                  int64_t ldx, double* __restrict__ y, int64_t ldy,
                                                  const Segment* __restrict__ segs, Segment one, int n_segs, int C,
-                                                 const double* __restrict__ state_in, double* __restrict__ state_out) {
+                                                 const double* __restrict__ state_in, double* __restrict__ state_out,
+                                                 const Segment* __restrict__ ysegs = nullptr) {
   const int cg = (C + 31) / 32;
   const int warp = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
   if (warp >= n_segs * cg) return;
   const int seg = warp / cg, c = (warp % cg) * 32 + (threadIdx.x & 31);
   if (c >= C) return;
   const Segment sg = segs ? segs[seg] : one;
+  // ysegs: where each segment's filtered rows go (segments may overlap in x: every one gets its own rows of y)
+  const int64_t y_row0 = ysegs ? ysegs[seg].row0 : sg.row0;
   double z0[kMaxSec], z1[kMaxSec];
 #pragma unroll
   for (int s = 0; s < kMaxSec; ++s) {
@@ -31,7 +34,7 @@ __global__ void __launch_bounds__(128) k_iir_seq(const __grid_constant__ Cascade
     z1[s] = state_in ? (s < q.ns ? state_in[(int64_t)(2 * s + 1) * C + c] : 0.0) : q.zi1[s];
   }
   const double* xp = x + sg.row0 * ldx + c;
-  double* yp = y + sg.row0 * ldy + c;
+  double* yp = y + y_row0 * ldy + c;
   constexpr int U = 8;
   int64_t t = 0;
   for (; t + U <= sg.T; t += U) {
@@ -507,6 +510,21 @@ __global__ void k_stats_merge(double* __restrict__ acc, const double* __restrict
   acc[c] = a.n;
   acc[C + c] = a.mean;
   acc[2 * C + c] = a.m2;
+}
+// Day-baseline exchange in one launch: gathered = (n_src, n_days, 3, C) accumulators (rank-major, as all-gathered); for
+// every (day, channel) the n_src accumulators are merged in source order (the same on every rank -> bit-identical results)
+// and finalised: mu = mean, sigma = sqrt(M2 / n) (np.std, ddof = 0).  Days nobody contributed to get mu = 0, sigma = 1.
+__global__ void k_stats_merge_days(const double* __restrict__ gathered, int n_src, int n_days, int C, double* __restrict__ mu,
+                                   double* __restrict__ sigma) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, d = blockIdx.y;
+  if (c >= C || d >= n_days) return;
+  Moments a{0.0, 0.0, 0.0};
+  for (int r = 0; r < n_src; ++r) {
+    const double* p = gathered + ((int64_t)r * n_days + d) * 3 * C;
+    a = chan_merge(a, Moments{p[c], p[C + c], p[2 * C + c]});
+  }
+  mu[(int64_t)d * C + c] = a.n > 0.0 ? a.mean : 0.0;
+  sigma[(int64_t)d * C + c] = a.n > 0.0 ? sqrt(a.m2 / a.n) : 1.0;
 }
 __global__ void k_stats_finalize(const double* __restrict__ acc, int C, double* __restrict__ mu,
                                  double* __restrict__ sigma) {

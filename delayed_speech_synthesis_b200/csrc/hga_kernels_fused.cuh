@@ -82,11 +82,6 @@ struct FusedArgs {
   double* state_out;      // (n_segs, ns, 2, C) or nullptr
   double* remainder_out;  // (n_segs, L - hop, C) or nullptr: last L-hop filtered rows of each segment
   int64_t x_row_lo, x_row_hi;  // rows [x_row_lo, x_row_hi) of x are addressable (TMA extents of the pipe kernel)
-  long long* prof;             // optional (HGA_B200_PROF=1): per-warp cycle breakdown of the pipe kernel, [n_cta][8 warps][6]
-  // k_hga_pipe2: zero-input response of the reference's initial state (sosfilt_zi of both filters), divided by the gain
-  // product, n_zir rows (a multiple of the hop, zero-padded); added to the first n_zir filtered rows of fresh items.
-  const double* zir;
-  int n_zir;
 };
 
 // Thread per (work item, channel); a warp spans 32 adjacent channels so every row access is one 256-byte segment.

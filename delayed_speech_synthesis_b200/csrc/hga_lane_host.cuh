@@ -358,6 +358,10 @@ struct LaneDev {  // device copies of a LanePlan and the scratch it needs (owned
   const LaneSub* subs = nullptr;  // LaneFixPlan (per handle)
   int n_sub = 0;
   const double* P = nullptr;
+  // partial launches (host-buffer path: the items whose rows have arrived): `order` then points into an item list of the
+  // caller's and n_items counts its entries; the fix-up kernels run once, after the last part
+  int n_items = -1;       // -1: all items of the plan
+  bool skip_fix = false;
 };
 
 typedef CUresult (*LaneEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -378,7 +382,7 @@ inline void lane_fill_args(const LanePlan& p, const LaneDev& d, int C, const dou
   a.work = d.work;
   a.n_work = (int)p.work.size();
   a.groups = p.groups;
-  a.n_items = a.n_work * p.groups;
+  a.n_items = d.n_items >= 0 ? d.n_items : a.n_work * p.groups;
   a.C = C;
   a.CP = p.groups * p.cw;
   a.mu = mu;
@@ -398,7 +402,7 @@ template <typename TY, int HOP>
 inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev& d, int C, const double* mu, const double* sigma, double* out, int64_t ldo,
                            cudaStream_t st) {
   const int n_fix = (int)p.fix.size();
-  if (n_fix == 0) return 0;
+  if (n_fix == 0 || d.skip_fix) return 0;
   const int CP = p.groups * p.cw;
   int launches = 0;
   const double* s0 = d.E;

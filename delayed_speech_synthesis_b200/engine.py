@@ -113,6 +113,13 @@ class HgaEngine:
     def stream_frames(self, n: int) -> int:
         return int(self._lib.hga_stream_frames(self._h, int(n)))
 
+    def last_plan(self) -> dict:
+        """How the last `extract_offline*` call was cut into time-chunks: rows per chunk, chunks, chunks that started from a
+        carried filter state, rows the carry reaches."""
+        rows, n, nc, k = C.c_int64(0), C.c_int32(0), C.c_int32(0), C.c_int32(0)
+        check(self._lib.hga_last_plan(self._h, C.byref(rows), C.byref(n), C.byref(nc), C.byref(k)))
+        return {"chunk_rows": rows.value, "chunks": n.value, "carried": nc.value, "carry_rows": k.value}
+
     def set_timing(self, on: bool) -> None:
         check(self._lib.hga_set_timing(self._h, int(on)))
 
@@ -139,6 +146,8 @@ class HgaEngine:
         if isinstance(x, torch.Tensor):
             if not x.is_cuda or x.dtype != torch.float64 or x.dim() != 2 or x.stride(1) != 1:
                 raise ValueError("device input must be a CUDA float64 (T, C) tensor with unit channel stride")
+            if x.shape[1] != self.n_channels:   # the reference's sosfilt raises on the zi shape mismatch
+                raise ValueError(f"expected {self.n_channels} channels, got {x.shape[1]}")
             start, length, frames, out_row = self._segments(x.shape[0], segments)
             total = int(sum(frames))
             if out is None:
@@ -154,6 +163,8 @@ class HgaEngine:
                                                 out.data_ptr(), out.stride(0), _stream_ptr(self.device)))
             return out
         x = _host_f64(x, "data")
+        if x.shape[1] != self.n_channels:
+            raise ValueError(f"expected {self.n_channels} channels, got {x.shape[1]}")
         start, length, frames, out_row = self._segments(x.shape[0], segments)
         total = int(sum(frames))
         if out is None:
@@ -207,6 +218,8 @@ class HgaEngine:
         if isinstance(x, torch.Tensor):
             if not x.is_cuda or x.dtype != torch.float64 or x.dim() != 2 or x.stride(1) != 1:
                 raise ValueError("device input must be a CUDA float64 (n, C) tensor with unit channel stride")
+            if x.shape[1] != self.n_channels:
+                raise ValueError(f"expected {self.n_channels} channels, got {x.shape[1]}")
             frames = self.stream_frames(x.shape[0])
             out = torch.empty((max(frames, 1), self.n_channels), dtype=torch.float64, device=x.device)[:frames]
             mu_t = sg_t = None

@@ -42,14 +42,21 @@ enum hga_precision {
    * in row order: bit-identical to scipy.signal.sosfilt (x2) -> compute_log_power_features up to the final log()
    * (CUDA log is <= 1 ulp; glibc's is correctly rounded in almost all cases).  Used for streaming and short trials. */
   HGA_PREC_EXACT = 0,
-  /* float64 with fused multiply-adds, time-chunked (each chunk re-filters `warmup` samples of history from zero
-   * state), window power as the sum of hop-block partial sums.  |feature - reference| <= 1e-9 (tests state it). */
+  /* float64 with fused multiply-adds.  A recording is cut into time-chunks that are filtered in parallel from zero state;
+   * the filter state is then carried from chunk to chunk exactly (end state -> zero-input response added to the head of
+   * the next chunk, down to `carry_tol` of the state), window power as the sum of hop-block partial sums.
+   * |feature - reference| <= 1e-9 whatever the out-of-band content of the input (tests state it; typical 1e-12). */
   HGA_PREC_F64 = 1,
-  /* float32 cascade arithmetic on the float64 input (converted after the load), float64 power sums / log / z-score,
-   * same time-chunking as HGA_PREC_F64.  Offline extraction only (streaming pushes keep HGA_PREC_EXACT arithmetic).
-   * |feature - reference| <= 1e-4 on white / ECoG-like input (tests state it; typical max 2e-5).  Needs the standard
-   * cascade (8 + 8 unit-numerator sections), hop 10 or 20, x 16-byte aligned with an even leading dimension. */
-  HGA_PREC_F32 = 2
+  /* float32 cascade arithmetic (two channels per register, fma.rn.f32x2) on the float64 input, float32 power sums / log /
+   * z-score, same chunking and carry.  Offline extraction only (streaming pushes keep HGA_PREC_EXACT arithmetic).
+   * |feature - reference| <= 1e-4 at 1 kHz, <= 5e-4 at 2 kHz on white / ECoG-like input (tests state it; typical 2e-5 /
+   * 1e-4).  Needs the standard cascade (8 + 8 unit-numerator sections, zi = sosfilt_zi), L = 5 hops, hop 10 or 20, x
+   * 16-byte aligned with an even leading dimension. */
+  HGA_PREC_F32 = 2,
+  /* float32 band-pass (poles <= 0.963, FMA pipe) + float64 notch (poles at 0.9976 - 0.9988, FP64 pipe), float64 power sums /
+   * log / z-score.  |feature - reference| <= 5e-5 at 1 kHz, <= 2e-4 at 2 kHz (typical 1e-5 / 4e-5).  Same requirements
+   * as HGA_PREC_F32. */
+  HGA_PREC_MIXED = 3
 };
 
 /* Configuration of one extractor = the constructor arguments of HighGammaExtractor (local/units.py:102-132) after the
@@ -70,9 +77,10 @@ typedef struct hga_config {
                                             NOT scaled by x[0] (local/units.py:128-132) */
   double zi_notch[HGA_MAX_SECTIONS * 2];
   int32_t precision;                     /* enum hga_precision: arithmetic of hga_extract_offline* */
-  int32_t warmup;                        /* HGA_PREC_F64: history re-filtered per time-chunk; 0 = derive from
-                                            warmup_tol and the largest pole radius */
-  double warmup_tol;                     /* target truncation error of the warm-up (0 = default: 1e-12 for F64, 1e-7 for F32) */
+  int32_t warmup;                        /* generic float64 kernel only (non-standard cascades, odd leading dimensions): history
+                                            re-filtered per time-chunk; 0 = derive from warmup_tol and the largest pole radius */
+  double warmup_tol;                     /* carry_tol: relative size at which a section's zero-input response is dropped from the
+                                            chunk-to-chunk carry (0 = default: 1e-11 F64, 1e-6 F32, 1e-7 MIXED) */
   int32_t max_push_rows;                 /* largest n accepted by hga_stream_push (0 = 4096) */
   int32_t reserved;
 } hga_config;
@@ -91,8 +99,11 @@ int hga_destroy(hga_handle* h);
 /* A fresh extractor: zi re-tiled, frame buffer zeroed and re-armed (WarmStartFrameBuffer.reset, pyx:90-94; the
  * reference gets the same effect by constructing a new extractor per trial, prepare_corpus.py:48). */
 int hga_reset(hga_handle* h, void* stream);
-/* Effective warm-up length (samples) the handle uses in HGA_PREC_F64 mode. */
+/* Rows at the head of a time-chunk that the carried state still reaches (the generic kernel: rows of re-filtered history). */
 int hga_warmup(const hga_handle* h);
+/* How the last hga_extract_offline* call on this handle was cut (for tests and reports): rows per time-chunk, number of
+ * chunks, number of chunks that started from a carried state, rows the carry reaches.  Any pointer may be NULL. */
+int hga_last_plan(const hga_handle* h, int64_t* chunk_rows, int32_t* n_chunks, int32_t* n_carried, int32_t* carry_rows);
 
 /* ---- offline: batched independent segments (prepare_corpus.py:42-52; baseline_offline.py:45-50) ------------------ */
 /* Frames a single call on `rows` filtered rows yields: compute_log_power_features' count (hga_optimized.pyx:36),
@@ -106,8 +117,11 @@ int64_t hga_num_frames(const hga_handle* h, int64_t rows);
 int hga_extract_offline(hga_handle* h, const double* x_dev, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
                         const int64_t* seg_len, const int64_t* out_row, const double* mu_dev, const double* sigma_dev,
                         double* out_dev, int64_t ldo, void* stream);
-/* Same with HOST buffers (x, mu, sigma, out): stages through pinned memory, overlapping the host<->device copies of
- * consecutive time slabs with the kernels; returns when `out_host` is complete. */
+/* Same with HOST buffers (x, mu, sigma, out).  The recording goes up in time slabs on a copy stream while the kernels run
+ * on the chunks that have arrived and finished frames go down.  Pageable host memory is staged through two pinned buffers
+ * owned by the handle (memcpy of slab k + 1 overlaps the DMA of slab k); page-locked memory (cudaHostAlloc /
+ * cudaHostRegister, detected with cudaPointerGetAttributes) is read by the DMA engine where it lies.  Returns when
+ * `out_host` is complete. */
 int hga_extract_offline_host(hga_handle* h, const double* x_host, int64_t ldx, int32_t n_segments,
                              const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
                              const double* mu_host, const double* sigma_host, double* out_host, int64_t ldo);
@@ -173,6 +187,11 @@ int hga_stats_merge(int32_t device, double* acc_a_dev, const double* acc_b_dev, 
                     void* stream);
 int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t C, double* mu_dev, double* sigma_dev,
                        void* stream);
+/* The day-baseline exchange of a sharded corpus in one launch (prepare_corpus.py:183-199 over ranks): gathered_dev holds
+ * (n_src, n_days, 3, C) accumulators, rank-major as an all-gather leaves them; per (day, channel) they are merged in source
+ * order (identical on every rank) and finalised into mu_dev / sigma_dev, each (n_days, C).  Days without frames: 0 / 1. */
+int hga_stats_merge_days(int32_t device, const double* gathered_dev, int32_t n_src, int32_t n_days, int32_t C, double* mu_dev,
+                         double* sigma_dev, void* stream);
 
 /* ---- channel-axis transforms either side of the path -------------------------------------- */
 /* One row-wise map  out[t, j] = alpha[j] * x[t, sel[j]] + beta[j] * mean_{c in group grp[j]} x[t, c]  covers

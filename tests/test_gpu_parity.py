@@ -2,12 +2,14 @@
 inputs.  Tolerances (stated here, per feature = per (frame, channel) element):
   * 'exact' precision and every streaming push <= 1024 rows: the arithmetic is the reference's, only the final log()
     may differ by one ulp  ->  max-abs <= 4e-15, max-rel <= 4e-15 on features (|f| < 8).
-  * 'f64' precision (fused multiply-adds, hop-block sums, warm-up truncation 1e-10): max-abs <= 1e-9 on features,
-    <= 5e-9 on z-scores (division by sigma ~ 0.4); relative error <= 1e-8 where |f| > 1e-2.
+  * 'f64' precision (fused multiply-adds, hop-block sums, chunked scan with the filter state carried to 1e-11): max-abs
+    <= 1e-9 on features, <= 5e-9 on z-scores (division by sigma ~ 0.4); relative error <= 1e-8 where |f| > 1e-2; also on
+    input with a DC offset 10^3 times the in-band amplitude (the carry propagates states, it does not re-estimate them).
   * filtered samples (hga_sosfilt) and filter states: bit-identical to scipy.signal.sosfilt.
   * baseline mu / sigma: relative error <= 1e-12.
-  * 'f32' precision (float32 cascade arithmetic, float64 power sums): max-abs <= 1e-4 on features (observed ~2e-5),
-    <= 5e-4 on z-scores.
+  * 'f32' precision (float32 cascade arithmetic and power sums): max-abs <= 1e-4 on features (observed ~2e-5),
+    <= 5e-4 on z-scores; at 2 kHz (notch poles at radius 0.9988) <= 5e-4 on features.
+  * 'mixed' precision (float32 band-pass, float64 notch): max-abs <= 5e-5 on features at 1 kHz, <= 2e-4 at 2 kHz.
 """
 import numpy as np
 import pytest
@@ -20,6 +22,7 @@ from oracle import c_oracle as CO  # noqa: E402
 TOL_EXACT = 4e-15
 TOL_F64 = 1e-9
 TOL_F32 = 1e-4
+TOL_MIX = 5e-5
 
 
 def _oracle_offline(x, fs, mu=None, sigma=None, segments=None):
@@ -72,21 +75,23 @@ def test_log_power_matches_reference_function(rows, C, fs):
 
 
 @pytest.mark.parametrize("rows,C,fs", [(60_000, 128, 1000), (7_777, 33, 2000), (50, 5, 1000), (1_290, 64, 1000), (200_013, 40, 1000)])
-def test_log_power_rolling_sums_are_bit_identical_to_the_window_loop(rows, C, fs, monkeypatch):
-    """k_frames_roll (one load per sample, five live sums) against k_frames_seq (thread per window) and the oracle's row-order
-    loop: every sum receives its rows in the same order, so the bits agree; with the fused z-score too."""
+def test_log_power_rolling_sums_are_bit_identical_to_the_window_loop(rows, C, fs):
+    """k_frames_roll (one load per sample, five live sums) against k_frames_seq (thread per window; taken for the frame
+    buffer's zero-padded geometry) on the same logical rows, and against the oracle's row-order loop: every sum receives
+    its rows in the same order, so the bits agree; with the fused z-score too."""
     from delayed_speech_synthesis_b200 import ops
     data = O.synthetic_ecog(rows, C, fs, "ecog", session=6)
+    hop = int(0.01 * fs)
+    padded = np.concatenate([np.zeros((hop, C)), data])            # rows the zero-padded call sees implicitly
     mu, sigma = np.linspace(1.0, 2.0, C), np.linspace(0.5, 1.5, C)
-    roll = ops.log_power(data, fs, 0.05, 0.01)
-    roll_z = ops.log_power(data, fs, 0.05, 0.01, mu, sigma)
-    monkeypatch.setenv("HGA_B200_FRAMES_ROLL", "0")
-    seq = ops.log_power(data, fs, 0.05, 0.01)
-    seq_z = ops.log_power(data, fs, 0.05, 0.01, mu, sigma)
-    assert roll.shape == seq.shape == ((rows - int(0.05 * fs)) // int(0.01 * fs) + 1, C)
+    roll = ops.log_power(padded, fs, 0.05, 0.01)
+    roll_z = ops.log_power(padded, fs, 0.05, 0.01, mu, sigma)
+    seq = ops.log_power(data, fs, 0.05, 0.01, zero_rows=hop)
+    seq_z = ops.log_power(data, fs, 0.05, 0.01, mu, sigma, zero_rows=hop)
+    assert roll.shape == seq.shape == ((rows + hop - int(0.05 * fs)) // hop + 1, C)
     assert np.array_equal(roll, seq) and np.array_equal(roll_z, seq_z)
     n = min(len(roll), 300)
-    ref = O.compute_log_power_features(data[:(n - 1) * int(0.01 * fs) + int(0.05 * fs)], fs, 0.05, 0.01)
+    ref = O.compute_log_power_features(padded[:(n - 1) * hop + int(0.05 * fs)], fs, 0.05, 0.01)
     assert _err(roll[:n], ref)[0] <= TOL_EXACT
 
 
@@ -176,7 +181,7 @@ def test_offline_time_chunked_long(torch):
     assert a <= TOL_F64, (a, r)
 
 
-@pytest.mark.parametrize("cfg,precision", [("k2", "f64"), ("k2", "f32"), ("k4", "f64"), ("k4", "f32")])
+@pytest.mark.parametrize("cfg,precision", [("k2", "f64"), ("k2", "f32"), ("k2", "mixed"), ("k4", "f64"), ("k4", "f32")])
 def test_offline_full_size_windows(cfg, precision, torch):
     """BASELINE configs 2 and 4 at full size (128 ch x 1 h @ 1 kHz = 3.69 GB; 1024 ch x 10 min @ 2 kHz = 9.83 GB), generated
     on the device: the start of the recording against a fresh-start oracle, and windows at seeded positions anywhere in
@@ -185,16 +190,22 @@ def test_offline_full_size_windows(cfg, precision, torch):
     from delayed_speech_synthesis_b200.engine import HgaEngine
     fs, T, C, lead, span, n_win = {"k2": (1000, 3_600_000, 128, 14000, 1000, 6), "k4": (2000, 1_200_000, 1024, 28000, 1000, 3)}[cfg]
     L, hop = int(0.05 * fs), int(0.01 * fs)
-    tol = TOL_F64 if precision == "f64" else (TOL_F32 if fs == 1000 else 5 * TOL_F32)
+    tol = TOL_F64 if precision == "f64" else (TOL_MIX if precision == "mixed" else (TOL_F32 if fs == 1000 else 5 * TOL_F32))
     g = torch.Generator(device="cuda").manual_seed(20241104)
     x = torch.randn((T, C), dtype=torch.float64, device="cuda", generator=g)
-    feats = HgaEngine(fs, C, precision=precision).extract_offline(x)
+    eng = HgaEngine(fs, C, precision=precision)
+    feats = eng.extract_offline(x)
     assert feats.shape == ((T - L) // hop + 1, C)
+    plan = eng.last_plan()
+    assert plan["carried"] >= 8, plan
     n0 = 60000 if cfg == "k2" else 20000
     ref = _oracle_offline(x[:n0].cpu().numpy(), fs)
     assert _err(feats[:len(ref)].cpu().numpy(), ref)[0] <= tol
     rng = np.random.Generator(np.random.Philox(key=[20241104, 99]))
-    for t0 in sorted(int(v) * hop for v in rng.integers(lead // hop, (T - span) // hop, size=n_win)) + [T - span]:
+    Lc = plan["chunk_rows"]
+    n_ch = -(-T // Lc)                                                                 # chunks of the one segment
+    seams = [k * Lc - span // 2 for k in (-(-(lead + span) // Lc), n_ch // 2, n_ch - 1)]   # windows ON chunk seams
+    for t0 in sorted(int(v) * hop for v in rng.integers(lead // hop, (T - span) // hop, size=n_win)) + seams + [T - span]:
         ref = _oracle_offline(x[t0 - lead:t0 + span].cpu().numpy(), fs)      # frame k of the slice = frame (t0 - lead) / hop + k
         k0 = lead // hop
         got = feats[t0 // hop:t0 // hop + (span - L) // hop + 1].cpu().numpy()
@@ -202,37 +213,112 @@ def test_offline_full_size_windows(cfg, precision, torch):
     assert bool(torch.isfinite(feats).all())
 
 
-@pytest.mark.parametrize("variant,S,TB", [("0", "4", "40"), ("1", "4", "40"), ("1", "2", "40"), ("1", "4", "20"), ("1", "4", "60"), ("1", "4", "80"), ("1", "8", "20")])
-def test_offline_kernel_variants_agree(variant, S, TB, torch, monkeypatch):
-    """The thread-sequential and the section-pipelined kernels (every warps-per-item / tile shape) against the oracle:
-    ragged segments (partial tiles, lengths that are not hop multiples), C not a multiple of 32, z-score."""
+@pytest.mark.parametrize("precision,tol,pad", [("f64", TOL_F64, 0), ("f64", TOL_F64, 1), ("f32", TOL_F32, 0), ("mixed", TOL_MIX, 0)])
+def test_offline_ragged_segments_every_kernel(precision, tol, pad, torch):
+    """The lane kernels (pad = 0) and the generic thread-sequential kernel (pad = 1: an odd leading dimension cannot be a
+    TMA tensor) against the oracle: ragged segments (partial tiles, lengths that are not hop multiples, the minimum length L),
+    C not a multiple of 32 or 64, z-score."""
     from delayed_speech_synthesis_b200.engine import HgaEngine
-    monkeypatch.setenv("HGA_B200_VARIANT", variant)
-    monkeypatch.setenv("HGA_B200_PIPE_S", S)
-    monkeypatch.setenv("HGA_B200_PIPE_TB", TB)
     fs, C = 1000, 70
     x = O.synthetic_ecog(90007, C, fs, "ecog", session=11)
     segs = [(0, 50), (50, 2590), (2600, 2655), (3000, 9017), (9018, 90007)]
     base = _oracle_offline(x, fs, segments=segs)
     mu, sigma = base.mean(0), base.std(0)
     ref = _oracle_offline(x, fs, mu, sigma, segments=segs)
-    got = HgaEngine(fs, C, precision="f64").extract_offline(torch.from_numpy(x).cuda(), segs, mu, sigma).cpu().numpy()
+    wide = torch.zeros((len(x), C + pad), dtype=torch.float64, device="cuda")
+    wide[:, :C] = torch.from_numpy(x).cuda()
+    eng = HgaEngine(fs, C, precision=precision)
+    got = eng.extract_offline(wide[:, :C], segs, mu, sigma).cpu().numpy()
     assert got.shape == ref.shape
-    assert _err(got, ref)[0] <= 5 * TOL_F64
+    assert _err(got, ref)[0] <= 5 * tol
+    assert (eng.last_plan()["chunk_rows"] > 0) == (pad == 0)      # which kernel ran
 
 
-def test_offline_caller_section_form_agrees(torch, monkeypatch):
-    """HGA_B200_FORM=64: the pipelined kernel with every section in the caller's [1, b1, 1] form and order (what a cascade
-    that cannot be re-paired into [1, 0, -1] sections gets) against the oracle, both precisions."""
+def test_offline_non_standard_cascade_takes_the_generic_kernel(torch):
+    """An order-4 band-pass (4 + 8 sections) is outside what the lane kernels are built for: the generic kernel runs the
+    caller's sections as given (float64 only; the packed / mixed arithmetic refuses)."""
+    from scipy.signal import iirfilter, sosfilt_zi
+    from delayed_speech_synthesis_b200 import HgaError
     from delayed_speech_synthesis_b200.engine import HgaEngine
-    monkeypatch.setenv("HGA_B200_FORM", "64")
-    fs, C = 1000, 128
-    x = O.synthetic_ecog(150000, C, fs, "ecog", session=13)
-    segs = [(0, 70000), (70000, 150000)]
+    fs, C = 1000, 40
+    x = O.synthetic_ecog(60000, C, fs, "ecog", session=13)
+    bp = iirfilter(4, np.array([70, 170]) / (fs / 2), btype="bandpass", ftype="butter", output="sos")
+    nt = O.design_hga_filters(fs)[1]
+    ref = CO.extract_fused(x, bp, sosfilt_zi(bp), nt, sosfilt_zi(nt), 50, 10)
+    eng = HgaEngine(fs, C, precision="f64", sos_bp=bp, sos_notch=nt)
+    got = eng.extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert _err(got, ref)[0] <= TOL_F64
+    assert eng.last_plan()["chunk_rows"] == 0
+    with pytest.raises(HgaError):
+        HgaEngine(fs, C, precision="f32", sos_bp=bp, sos_notch=nt).extract_offline(torch.from_numpy(x).cuda())
+
+
+@pytest.mark.parametrize("precision,tol", [("f64", TOL_F64), ("f32", 20 * TOL_F32), ("mixed", 20 * TOL_MIX)])
+def test_offline_dc_offset_across_chunk_seams(precision, tol, torch):
+    """Raw amplifier signals sit on per-channel offsets far above the high-gamma amplitude: +-5000 here against
+    an in-band RMS of ~5.  The filter states at a chunk seam scale with the offset; the carry propagates them exactly, so the
+    float64 bound holds unchanged (the float32 modes lose what float32 loses on the offset itself: tolerance x 20)."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, C = 1000, 400000, 64
+    x = O.synthetic_ecog(T, C, fs, "ecog", session=21)
+    x += np.linspace(-5000.0, 5000.0, C)[None, :]
+    ref = _oracle_offline(x, fs)
+    eng = HgaEngine(fs, C, precision=precision)
+    got = eng.extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    plan = eng.last_plan()
+    assert plan["carried"] >= 100, plan                                # the recording really was cut
+    a, r = _err(got, ref)
+    assert a <= tol, (a, r, plan)
+    # the frames around every seam, separately (where a state error would sit)
+    Lc, hop = plan["chunk_rows"], 10
+    seam = np.concatenate([np.arange(k * Lc // hop - 5, k * Lc // hop + 40) for k in range(1, plan["chunks"])])
+    seam = seam[seam < len(ref)]
+    assert np.abs(got[seam] - ref[seam]).max() <= tol
+
+
+def test_offline_exact_overlapping_segments(torch):
+    """Trials closer than the 40 ms tail overlap in x (prepare_corpus.py:49); every one is filtered from its own fresh
+    state, in every precision (the exact path used to share one scratch row per x row)."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, C = 1000, 33
+    x = O.synthetic_ecog(9000, C, fs, "ecog", session=17)
+    segs = [(0, 2540), (2500, 5040), (2520, 2600), (5000, 9000), (100, 8000)]
     ref = _oracle_offline(x, fs, segments=segs)
-    xd = torch.from_numpy(x).cuda()
-    assert _err(HgaEngine(fs, C, precision="f64").extract_offline(xd, segs).cpu().numpy(), ref)[0] <= TOL_F64
-    assert _err(HgaEngine(fs, C, precision="f32").extract_offline(xd, segs).cpu().numpy(), ref)[0] <= TOL_F32
+    for precision, tol in (("exact", TOL_EXACT), ("f64", TOL_F64), ("f32", TOL_F32)):
+        got = HgaEngine(fs, C, precision=precision).extract_offline(torch.from_numpy(x).cuda(), segs).cpu().numpy()
+        assert got.shape == ref.shape and _err(got, ref)[0] <= tol, precision
+        assert _err(HgaEngine(fs, C, precision=precision).extract_offline(x, segs), ref)[0] <= tol, precision
+
+
+@pytest.mark.parametrize("fs,kind,tol", [(1000, "white", TOL_MIX), (1000, "ecog", TOL_MIX), (2000, "white", 4 * TOL_MIX)])
+def test_offline_mixed_mode(fs, kind, tol, torch):
+    """float32 band-pass + float64 notch: stated tolerance 5e-5 per feature at 1 kHz, 2e-4 at 2 kHz."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    T, C = 200 * fs, 128
+    x = O.synthetic_ecog(T, C, fs, kind, session=14)
+    ref = _oracle_offline(x, fs)
+    mu, sigma = ref.mean(0), ref.std(0)
+    eng = HgaEngine(fs, C, precision="mixed")
+    got = eng.extract_offline(torch.from_numpy(x).cuda()).cpu().numpy()
+    a, r = _err(got, ref)
+    assert a <= tol, (a, r)
+    z = eng.extract_offline(torch.from_numpy(x).cuda(), None, mu, sigma).cpu().numpy()
+    assert np.abs(z - (ref - mu) / sigma).max() <= 5 * tol
+
+
+def test_offline_pageable_and_pinned_host_buffers_agree(torch):
+    """hga_extract_offline_host reads page-locked memory where it lies and stages pageable memory (what numpy hands over)
+    through its own pinned buffers: same bits either way, strided input and output included."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, C = 1000, 300000, 128
+    x = O.synthetic_ecog(T, C + 2, fs, "white", session=19)[:, 1:C + 1]        # pageable, leading dimension C + 2
+    eng = HgaEngine(fs, C, precision="f64")
+    a = eng.extract_offline(x)
+    xp = torch.from_numpy(np.ascontiguousarray(x)).pin_memory()
+    outp = torch.empty((eng.num_frames(T), C), dtype=torch.float64).pin_memory()
+    b = eng.extract_offline(xp.numpy(), out=outp.numpy())
+    assert np.array_equal(a, b)
+    assert _err(a, _oracle_offline(np.ascontiguousarray(x), fs))[0] <= TOL_F64
 
 
 @pytest.mark.parametrize("kind", ["white", "ecog"])
@@ -298,6 +384,28 @@ def test_streaming_matches_oracle_unit(chunks):
         t += n
     assert np.array_equal(ex.hg_state, ref_ex.hg_state)
     assert np.array_equal(ex.fh_state, ref_ex.fh_state)
+
+
+def test_streaming_long_lived_handle_10500_packets():
+    """BASELINE config 3 / SURVEY 8d: >= 10 500 ten-sample pushes on ONE handle (105 s of signal).  Frames within the
+    reference-order bound of the oracle's filtering + framing of the whole signal (streaming == offline on
+    [40 zero rows; y], SURVEY 8c pin (i)); the carried filter states bit-equal to scipy's after the last packet."""
+    from scipy.signal import sosfilt, sosfilt_zi
+    from delayed_speech_synthesis_b200.common import ZScoreNormalization
+    from delayed_speech_synthesis_b200.units import HighGammaExtractor
+    fs, C, n_pk, n = 1000, 128, 10500, 10
+    x = O.synthetic_ecog(n_pk * n, C, fs, "ecog", session=23)
+    rng = np.random.default_rng(1)
+    mu, sigma = rng.normal(3, 1, (1, C)), rng.uniform(0.3, 0.6, (1, C))
+    ex = HighGammaExtractor(fs, C, post_transforms=[ZScoreNormalization(mu, sigma)])
+    frames = np.concatenate([ex.extract_features(x[i * n:(i + 1) * n]) for i in range(n_pk)])
+    bp, nt = O.design_hga_filters(fs)
+    y, z_bp = sosfilt(bp, x, axis=0, zi=O.tiled_zi(bp, C))
+    y, z_nt = sosfilt(nt, y, axis=0, zi=O.tiled_zi(nt, C))
+    ref = (O.compute_log_power_features_fast(np.concatenate([np.zeros((40, C)), y]), fs, 0.05, 0.01) - mu) / sigma
+    assert frames.shape == ref.shape == (n_pk, C)
+    assert _err(frames, ref)[0] <= 25 * TOL_EXACT          # z-score divides the ulp of log() by sigma >= 0.3
+    assert np.array_equal(ex.hg_state, z_bp) and np.array_equal(ex.fh_state, z_nt)
 
 
 def test_streaming_equals_offline_with_zero_pad():
