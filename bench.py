@@ -1,13 +1,19 @@
 #!/usr/bin/env python
 """bench.py — HGA channel-samples/s on B200 (BASELINE.json metric), one process per GPU.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload k2|k4|k1]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--precision f32|f64|mixed]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
-A step = one pass of the hot path (IIR cascade + framing + log-power + z-score) over one resident recording per rank
-(default K2: 128 ch x 1 h @ 1 kHz, float64, 3.69 GB > L2, so no L2 flush is needed between steps).  Ranks hold
-different recordings (weak scaling, no data-path collective); the day-baseline (mu, sigma) are computed before the timed
-region from a 60 s baseline prefix per rank, combined over ranks by an NCCL all-gather + fixed-order Chan merge.
+N = 1 (BASELINE config 2, "k2"): a step = one pass of the hot path (IIR cascade + framing + log-power + z-score) over one
+resident recording, 128 ch x 1 h @ 1 kHz float64 (3.69 GB > L2: no flush needed between steps).  `value` = device-resident
+throughput, `e2e` = the same call on HOST buffers (copies inside the timed region).  Side entries of the same line: the other
+precisions, short recordings (k1, 10 min), k4, the k5 corpus on one GPU, streaming latency (k3), the CPU baseline.
+
+N > 1 (BASELINE config 5, "k5"): a step = the whole corpus build of prepare_corpus.py:179-236 on 64 sessions x 128 ch x 1 h
+dealt round-robin to the ranks: per-day baseline statistics from the baseline sessions, ONE NCCL all-gather of all days'
+(n, mean, M2) + fixed-order merge, then every owned session extracted and z-scored.  Everything is inside the timed region;
+strong scaling (the corpus is fixed).  Parity (mu / sigma identical on every rank and equal to numpy over the baseline
+features; one session's features equal to a single-GPU recomputation) is asserted outside the timed region (`parity_ok`).
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
@@ -28,11 +34,15 @@ sys.path.insert(0, str(ROOT))
 
 WORKLOADS = {  # name: (fs, channels, seconds)
     "k1": (1000, 128, 60),
+    "m10": (1000, 128, 600),
     "k2": (1000, 128, 3600),
     "k4": (2000, 1024, 600),
 }
+K5_SESSIONS, K5_DAYS = 64, 8          # 8 days x 8 sessions; session 0 of each day is its baseline
 METRIC = "hga_channel_samples_per_s"
 UNIT = "channel-samples/s"
+TOLERANCE = {"f64": "max-abs 1e-9 per feature vs the float64 oracle", "f32": "max-abs 1e-4 per feature (5e-4 at 2 kHz)",
+             "mixed": "max-abs 5e-5 per feature (2e-4 at 2 kHz)"}
 
 
 def peaks():
@@ -42,8 +52,18 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def workload_name(w):
+    fs, C, secs = WORKLOADS[w]
+    return f"{w}: {C} ch x {secs} s @ {fs} Hz float64, band-pass+notch cascade, 50ms/10ms log-power, z-score"
+
+
+def k5_name():
+    return (f"k5: {K5_SESSIONS} sessions x 128 ch x 3600 s @ 1000 Hz float64 ({K5_DAYS} days, session 0 of a day = its baseline), per-day "
+            "baseline statistics + all-gather + fixed-order merge + extraction + z-score of every session")
+
+
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -85,92 +105,196 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the reference's own CPU composition (scipy sosfilt x2 -> compiled reference extension
-# compute_log_power_features -> numpy z-score), see oracle/.
+# compute_log_power_features -> numpy z-score, local/units.py:151-160), see oracle/.  The composition is single-threaded
+# and channels never mix, so "all host cores" = one worker process per block of channels.  A worker builds its block ONCE
+# (pool initializer) and returns a checksum per step: nothing but an index and a float crosses the process boundary inside
+# the timed region (round 1 pickled the 7.7 MB blocks on every step and measured the pipe, not the filters).
 # ----------------------------------------------------------------------------------------------------------------------
-def _ref_worker(args):
-    x, fs, mu, sigma = args
+def _host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def _ref_worker(k, fs, n_rows, cols, seed, start, done, stop, sums):
+    """Worker k owns channel block `cols` for its whole life: generate once, then one extraction per start/done barrier pair."""
     from oracle import build_ref, hga_oracle as O
     ref = build_ref.load()
-    ex = O.HighGammaExtractor(fs, x.shape[1], log_power=(ref.compute_log_power_features if ref is not None
-                                                          else O.compute_log_power_features_fast))
-    f = ex.extract_features(x)
-    return (f - mu) / sigma
+    log_power = ref.compute_log_power_features if ref is not None else O.compute_log_power_features_fast
+    rng = np.random.Generator(np.random.Philox(key=[seed, int(cols[0])]))
+    x = rng.standard_normal((n_rows, len(cols)))
+    x += (5.0 * np.sin(2 * np.pi * 120.0 * np.arange(n_rows) / fs))[:, None]
+    while True:
+        start.wait()
+        if stop.is_set():
+            return
+        f = O.HighGammaExtractor(fs, x.shape[1], log_power=log_power).extract_features(x)     # local/units.py:151-156
+        sums[k] = float(((f - 3.0) / 0.4).sum())                                                # prepare_corpus.py:226-227
+        done.wait()
 
 
-def reference_rate(fs: int, C: int, seconds: int, procs: int, budget_s: float, min_reps: int = 1):
-    """channel-samples/s of the reference composition on `procs` host processes (channels split across them)."""
-    from oracle import build_ref, hga_oracle as O
-    kind = "reference" if build_ref.load() is not None else "port"
-    x = O.synthetic_ecog(fs * seconds, C, fs, "white")
-    procs = max(1, min(procs, C))
-    blocks = np.array_split(np.arange(C), procs)
-    jobs = [(np.ascontiguousarray(x[:, b]), fs, np.full(len(b), 3.0), np.full(len(b), 0.4)) for b in blocks]
-    times = []
-    if procs == 1:
-        t_end = time.perf_counter() + budget_s
-        while len(times) < min_reps or time.perf_counter() < t_end:
-            t0 = time.perf_counter()
-            _ref_worker(jobs[0])
-            times.append(time.perf_counter() - t0)
-            if len(times) >= 50:
-                break
-    else:
+class ReferencePool:
+    """`procs` processes, each holding a block of channels of a (n_rows, C) recording."""
+
+    def __init__(self, fs, C, n_rows, procs):
         import multiprocessing as mp
-        with mp.get_context("fork").Pool(procs) as pool:
-            pool.map(_ref_worker, jobs)  # warm the workers
-            t_end = time.perf_counter() + budget_s
-            while len(times) < min_reps or time.perf_counter() < t_end:
-                t0 = time.perf_counter()
-                pool.map(_ref_worker, jobs)
-                times.append(time.perf_counter() - t0)
-                if len(times) >= 50:
-                    break
-    best = float(np.median(times))
-    return fs * seconds * C / best, kind, f"{C} ch x {seconds} s @ {fs} Hz white float64, median of {len(times)} runs"
+        from oracle import build_ref
+        self.kind = "reference" if build_ref.load() is not None else "port"
+        ctx = mp.get_context("fork")
+        self.procs = max(1, min(procs, C))
+        blocks = np.array_split(np.arange(C), self.procs)
+        self.start, self.done, self.stop = ctx.Barrier(self.procs + 1), ctx.Barrier(self.procs + 1), ctx.Event()
+        self.sums = ctx.Array("d", self.procs)
+        self.ps = [ctx.Process(target=_ref_worker, args=(k, fs, n_rows, blocks[k], 20241104, self.start, self.done, self.stop, self.sums), daemon=True)
+                   for k in range(self.procs)]
+        for p in self.ps:
+            p.start()
+        self.units = n_rows * C
+
+    def step(self):
+        """One pass of every worker over its block; returns the wall time between the two barriers."""
+        self.start.wait()
+        t0 = time.perf_counter()
+        self.done.wait()
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.stop.set()
+        self.start.wait()
+        for p in self.ps:
+            p.join(timeout=10)
+
+
+def reference_rate(fs, C, seconds, procs, steps, warm=1):
+    """channel-samples/s of the reference composition: median over `steps` passes of `procs` workers over a (seconds * fs, C)
+    recording (channels split across the workers)."""
+    pool = ReferencePool(fs, C, fs * seconds, procs)
+    try:
+        for _ in range(warm):
+            pool.step()
+        times = [pool.step() for _ in range(steps)]
+    finally:
+        pool.close()
+    return pool.units / float(np.median(times)), pool.kind, times
 
 
 def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    fs, C, secs = WORKLOADS[args.workload]
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    sample_s = 120 if fs * C <= 128000 else 15
-    from oracle import hga_oracle as O
-    x_fs = fs
-    times = []
-    # steps/warmup honoured: each step = one bounded sample across all cores
-    import multiprocessing as mp
-    from oracle import build_ref
-    kind = "reference" if build_ref.load() is not None else "port"
-    x = O.synthetic_ecog(fs * sample_s, C, fs, "white")
-    procs = max(1, min(cores, C))
-    blocks = np.array_split(np.arange(C), procs)
-    jobs = [(np.ascontiguousarray(x[:, b]), x_fs, np.full(len(b), 3.0), np.full(len(b), 0.4)) for b in blocks]
-    with mp.get_context("fork").Pool(procs) as pool:
-        for _ in range(max(1, args.warmup)):
-            pool.map(_ref_worker, jobs)
-        for _ in range(args.steps):
-            t0 = time.perf_counter()
-            pool.map(_ref_worker, jobs)
-            times.append(time.perf_counter() - t0)
+    fs, C, secs = WORKLOADS["k2"]
+    cores = _host_cores()
+    # N = 1: every step is one whole k2 recording (the GPU arm's step).  N > 1: the GPU arm's step is the 64-session corpus
+    # (64 x k2 = 29.5 G channel-samples, a minute of CPU time per step on this host): a step here is ONE session of it.
+    n_rows = fs * secs
+    pool = ReferencePool(fs, C, n_rows, cores)
+    procs, kind = pool.procs, pool.kind
+    try:
+        for _ in range(max(1, min(args.warmup, 2))):
+            pool.step()
+        times = [pool.step() for _ in range(args.steps)]
+    finally:
+        pool.close()
     ms = 1e3 * float(np.mean(times))
-    value = fs * sample_s * C / (ms / 1e3)
-    sample = f"{C} ch x {sample_s} s @ {fs} Hz white float64 per step, channels split over {procs} processes"
+    value = n_rows * C / (ms / 1e3)
+    one_core, _, _ = reference_rate(fs, max(1, C // procs), 60, 1, steps=3)   # one worker's share of the channels, 60 s, one core
+    sample = (f"{C} ch x {secs} s @ {fs} Hz white float64 per step (one whole k2 recording" +
+              ("" if world == 1 else f"; stands for one of the {K5_SESSIONS} sessions of k5") +
+              f"), channels split over {procs} worker processes that hold their block")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": {"workload": workload_name(args.workload), "sample": sample},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind, "sample": sample},
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name("k2") if world == 1 else k5_name(), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind, "sample": sample,
+                         "one_core_value": one_core, "parallel_efficiency": value / (procs * one_core)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
 
 
-def stream_latency(fs, C, mu, sigma, device, n_push=10000, warm=500, chunk=10):
-    """p50 / p99 per-packet latency (us) of hga_stream_push_host (the packet's way to the device, one kernel and the frame's
-    way back inside the timed call) and of the reference composition fed the same packets (bounded: 2000 packets)."""
+# ----------------------------------------------------------------------------------------------------------------------
+# B200 arm, shared pieces
+# ----------------------------------------------------------------------------------------------------------------------
+def make_recording(torch, dev, T, C, fs, seed):
+    """Synthetic recording generated on the device (Philox): white N(0, 1) + a 120 Hz line sitting in the notch."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(int(seed))
+    x = torch.empty((T, C), dtype=torch.float64, device=dev)
+    step_rows = max(1, (1 << 27) // C)
+    for r0 in range(0, T, step_rows):
+        x[r0:r0 + step_rows].normal_(generator=g)
+    x += (5.0 * torch.sin(2 * torch.pi * 120.0 * torch.arange(T, device=dev, dtype=torch.float64) / fs)).unsqueeze(1)
+    return x
+
+
+def time_steps(torch, fn, steps, warm, barrier=None):
+    """ms per call of fn(): `warm` untimed calls, then `steps` calls between two CUDA events on the current stream."""
+    for _ in range(warm):
+        fn()
+    if barrier:
+        barrier()
+    else:
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    if barrier:
+        barrier()
+    else:
+        torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def roofline_entry(C, T, hop, ms, hbm_peak):
+    bytes_per = 8.0 + 8.0 / hop
+    achieved = C * T * bytes_per / (ms / 1e3) / 1e9
+    return achieved, achieved / hbm_peak, bytes_per
+
+
+def profile_facts(precision):
+    """ncu facts of the committed capture of this round (profiles/r02_ncu_facts.json): DRAM traffic per launch and pipe
+    utilisation of the dominant kernel.  Not measured here (nothing in this file runs under a profiler)."""
+    p = ROOT / "profiles" / "r02_ncu_facts.json"
+    if p.exists():
+        return json.loads(p.read_text()).get(precision)
+    return None
+
+
+def bind_near_gpu(torch, local):
+    """Pin this process to the CPUs next to its GPU (first-touch then places pinned staging on that NUMA node)."""
+    try:
+        out = subprocess.run(["nvidia-smi", f"--id={local}", "--query-gpu=pci.bus_id", "--format=csv,noheader"], capture_output=True, text=True).stdout.strip()
+        bus = out[-12:].lower() if out else None          # 00000000:1B:00.0 -> 0000:1b:00.0 (sysfs name)
+        cpus = Path(f"/sys/bus/pci/devices/{str(bus).lower()}/local_cpulist").read_text().strip()
+        node = Path(f"/sys/bus/pci/devices/{str(bus).lower()}/numa_node").read_text().strip()
+        ids = set()
+        for part in cpus.split(","):
+            a, _, b = part.partition("-")
+            ids.update(range(int(a), int(b or a) + 1))
+        ids &= os.sched_getaffinity(0)
+        if ids:
+            os.sched_setaffinity(0, ids)
+        return {"pci": str(bus), "numa_node": node, "cpus": cpus, "bound": bool(ids)}
+    except Exception as exc:      # report, do not hide
+        return {"error": repr(exc)}
+
+
+def h2d_bandwidth(torch, dev, barrier=None, mib=512, reps=3):
+    """GB/s of a bare pinned host -> device copy on this rank (all ranks at once when a barrier is given)."""
+    h = torch.empty(mib << 20, dtype=torch.uint8, pin_memory=True)
+    d = torch.empty(mib << 20, dtype=torch.uint8, device=dev)
+    d.copy_(h, non_blocking=True)
+    ms = time_steps(torch, lambda: d.copy_(h, non_blocking=True), reps, 1, barrier)
+    return (mib << 20) / (ms / 1e3) / 1e9
+
+
+def stream_latency(fs, C, mu, sigma, device, n_push=10500, warm=500, chunk=10):
+    """p50 / p99 per-packet latency (us) of hga_stream_push_host on ONE long-lived handle (the packet's way to the device,
+    one kernel and the frame's way back inside the timed call), of the wire-packet call, and of the reference composition fed
+    the same packets (bounded: 2000 packets)."""
     from delayed_speech_synthesis_b200.engine import HgaEngine
+    from delayed_speech_synthesis_b200 import wire
     x = np.random.default_rng(20241104).standard_normal(((n_push + warm) * chunk, C))
     eng = HgaEngine(fs, C, precision="exact", device=device)
     lat = np.empty(n_push + warm)
@@ -180,8 +304,6 @@ def stream_latency(fs, C, mu, sigma, device, n_push=10000, warm=500, chunk=10):
         eng.push(pkt, mu, sigma)
         lat[i] = time.perf_counter() - t0
     lat = lat[warm:] * 1e6
-    # wire-packet path (hga_stream_push_packet): '=BBB HH' header + float32 channel-major payload, decode fused in the kernel
-    from delayed_speech_synthesis_b200 import wire
     n_pk = min(n_push, 4000)
     x32 = x[:(n_pk + warm) * chunk].astype(np.float32)
     pkts = [wire.pack_packet(x32[i * chunk:(i + 1) * chunk].T) for i in range(n_pk + warm)]
@@ -206,78 +328,239 @@ def stream_latency(fs, C, mu, sigma, device, n_push=10000, warm=500, chunk=10):
     rl = rl[200:] * 1e6
     return {"packet": f"{chunk} x {C} float64", "n": int(n_push), "p50_us": float(np.percentile(lat, 50)),
             "p99_us": float(np.percentile(lat, 99)), "max_us": float(lat.max()),
-            "path": "hga_stream_push_host: mapped pinned staging (zero-copy), 1 kernel (k_stream_push_sys), completion slots polled in mapped memory, exact arithmetic",
+            "path": "hga_stream_push_host on one long-lived handle: mapped pinned staging (zero-copy), 1 kernel (k_stream_push_sys), completion slots polled in mapped memory, exact arithmetic",
             "wire_packet": {"packet": f"7-byte header + {C} x {chunk} float32", "n": int(n_pk), "p50_us": float(np.percentile(lp, 50)),
                             "p99_us": float(np.percentile(lp, 99)), "path": "hga_stream_push_packet (interpret_bytes fused into the kernel)"},
             "reference_p50_us": float(np.percentile(rl, 50)), "reference_p99_us": float(np.percentile(rl, 99)),
             "reference_n": int(len(rl))}
 
 
-def workload_name(w):
-    fs, C, secs = WORKLOADS[w]
-    return f"{w}: {C} ch x {secs} s @ {fs} Hz float64, band-pass+notch cascade, 50ms/10ms log-power, z-score"
+def device_rate(torch, eng, x, mu, sigma, steps, warm=3):
+    """(ms per extraction, features) of the device-resident call on x."""
+    out = torch.empty((eng.num_frames(x.shape[0]), x.shape[1]), dtype=torch.float64, device=x.device)
+    ms = time_steps(torch, lambda: eng.extract_offline(x, None, mu, sigma, out=out), steps, warm)
+    return ms, out
+
+
+def side_workload(torch, dev, local, name, precisions, steps, hbm_peak):
+    """A further BASELINE configuration on the same GPU (short recordings, k4): channel-samples/s per precision."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, C, secs = WORKLOADS[name]
+    T = fs * secs
+    x = make_recording(torch, dev, T, C, fs, 777)
+    res = {"workload": workload_name(name), "input_bytes": T * C * 8,
+           "l2": "input > 126 MB L2" if T * C * 8 > (126 << 20) else "input fits the 126 MB L2 (recurring steps re-read it from L2)"}
+    for prec in precisions:
+        eng = HgaEngine(fs, C, precision=prec, device=local)
+        base = eng.extract_offline(x[: 60 * fs])
+        mu, sigma = base.mean(0), base.std(0, unbiased=False)
+        ms, _ = device_rate(torch, eng, x, mu, sigma, steps)
+        ach, frac, _ = roofline_entry(C, T, eng.hop, ms, hbm_peak)
+        res[prec] = {"value": C * T / (ms / 1e3), "ms_per_step": ms, "roofline_frac": frac, "plan": eng.last_plan()}
+        del eng
+    del x
+    torch.cuda.empty_cache()
+    return res
 
 
 # ----------------------------------------------------------------------------------------------------------------------
-def run_b200(args):
+# k5: the corpus build (prepare_corpus.py:179-236) on 64 sessions, sharded over the ranks
+# ----------------------------------------------------------------------------------------------------------------------
+class Corpus:
+    """The rank's share of k5.  Sessions are generated on the device from their id (so any rank can regenerate any session
+    for the parity check) and stay resident; a rank that owns more sessions than fit beside the scratch (N = 1: 64 x 3.69 GB
+    = 236 GB > 180 GB of HBM) keeps `n_buf` distinct recordings and session i of its list reads recording i % n_buf: every
+    extraction still streams 3.69 GB from HBM, only the content repeats."""
+
+    def __init__(self, torch, dev, local, rank, world, precision, max_buffers=32):
+        from delayed_speech_synthesis_b200 import corpus
+        from delayed_speech_synthesis_b200.engine import HgaEngine
+        from delayed_speech_synthesis_b200.ops import ChannelStats
+        self.torch, self.dev, self.local, self.rank, self.world = torch, dev, local, rank, world
+        self.fs, self.C, secs = WORKLOADS["k2"]
+        self.T = self.fs * secs
+        self.corpus, self.ChannelStats = corpus, ChannelStats
+        self.day_of = [s // (K5_SESSIONS // K5_DAYS) for s in range(K5_SESSIONS)]
+        self.baseline = [d * (K5_SESSIONS // K5_DAYS) for d in range(K5_DAYS)]
+        self.mine = corpus.shard_sessions(K5_SESSIONS, rank, world)
+        free, _ = torch.cuda.mem_get_info(dev)
+        per = self.T * self.C * 8
+        self.n_buf = max(1, min(len(self.mine), max_buffers, int((free - (14 << 30)) // per)))
+        self.buffers = [make_recording(torch, dev, self.T, self.C, self.fs, 5000 + s) for s in self.mine[:self.n_buf]]
+        self.eng = HgaEngine(self.fs, self.C, precision=precision, device=local)
+        self.out = torch.empty((self.eng.num_frames(self.T), self.C), dtype=torch.float64, device=dev)
+        self.units = K5_SESSIONS * self.C * self.T        # channel-samples of the corpus (the baseline pass is overhead)
+
+    def session(self, s):
+        return self.buffers[self.mine.index(s) % self.n_buf]
+
+    def extract(self, x, mu, sigma):
+        return self.eng.extract_offline(x, None, mu, sigma, out=self.out)
+
+    def accumulate(self, f):
+        return self.ChannelStats(self.C, self.local).update(f).acc
+
+    def step(self, timings=None, on_features=None):
+        return self.corpus.extract_corpus(K5_SESSIONS, self.day_of, self.baseline, self.session, self.extract, self.accumulate,
+                                          n_channels=self.C, device=self.local, on_features=on_features, timings=timings)
+
+    # ---- parity, outside the timed region
+    def parity(self, dist):
+        torch = self.torch
+        mu, sigma, slots = self.step()
+        ok, detail = True, {}
+        if self.world > 1:       # (1) bit-identical mu / sigma on every rank
+            both = torch.stack([mu, sigma]).contiguous()
+            allr = [torch.empty_like(both) for _ in range(self.world)]
+            dist.all_gather(allr, both)
+            detail["mu_sigma_identical_on_all_ranks"] = all(bool(torch.equal(allr[0], a)) for a in allr)
+            ok &= detail["mu_sigma_identical_on_all_ranks"]
+        worst = 0.0              # (2) against numpy over the baseline features of the days this rank owns the baseline of
+        for s in self.baseline:
+            if s in self.mine and self.mine.index(s) < self.n_buf:
+                f = self.extract(self.session(s), None, None).cpu().numpy()
+                d = slots[self.day_of[s]]
+                worst = max(worst, float(np.abs(mu[d].cpu().numpy() / f.mean(0) - 1).max()), float(np.abs(sigma[d].cpu().numpy() / f.std(0) - 1).max()))
+        t = torch.tensor([worst], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        detail["mu_sigma_max_rel_err_vs_numpy"] = float(t.item())
+        ok &= detail["mu_sigma_max_rel_err_vs_numpy"] <= 1e-12
+        # (3) one session of another rank, recomputed on rank 0 from its id with the merged statistics
+        s_chk = 1 if self.world > 1 else min(1, K5_SESSIONS - 1)
+        owner = s_chk % self.world
+        d = slots[self.day_of[s_chk]]
+        feats = torch.empty_like(self.out)
+        if self.rank == owner:
+            feats.copy_(self.extract(self.session(s_chk), mu[d], sigma[d]))
+        if self.world > 1:
+            dist.broadcast(feats, src=owner)
+        same = True
+        if self.rank == 0:
+            x = self.session(s_chk) if owner == 0 else make_recording(torch, self.dev, self.T, self.C, self.fs, 5000 + s_chk)
+            mine = self.extract(x, mu[d], sigma[d])
+            same = bool(torch.equal(mine, feats)) and bool(torch.isfinite(mine).all())
+            del x
+        t = torch.tensor([1.0 if same else 0.0], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.broadcast(t, src=0)
+        detail["session_features_equal_single_gpu"] = bool(t.item() == 1.0)
+        ok &= detail["session_features_equal_single_gpu"]
+        detail["checked_session"] = s_chk
+        return bool(ok), detail
+
+
+def corpus_timed(torch, cp, steps, warm, barrier):
+    """(ms per corpus step on this rank, mean ms of the statistics exchange inside it)."""
+    timings = {}
+    for _ in range(warm):
+        cp.step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        cp.step(timings)
+    e1.record()
+    barrier()
+    ev = timings.get("exchange_events", [])
+    exch = float(np.mean([a.elapsed_time(b) for a, b in ev])) if ev else None
+    return e0.elapsed_time(e1) / steps, exch
+
+
+def corpus_e2e(torch, cp, dist, steps, barrier):
+    """The same corpus step through the host-buffer C-ABI call: every session goes up from pinned host memory and its
+    features come down, inside the timed region.  One host recording per rank stands for all of its sessions (same bytes
+    through PCIe every time).  Returns (seconds per step, max over ranks; bytes up / down per step on this rank)."""
+    xh = torch.empty((cp.T, cp.C), dtype=torch.float64, pin_memory=True)
+    xh.copy_(cp.buffers[0])
+    oh = torch.empty((cp.eng.num_frames(cp.T), cp.C), dtype=torch.float64, pin_memory=True)
+    xn, on = xh.numpy(), oh.numpy()
+
+    def extract(x, mu, sigma):
+        m = None if mu is None else mu.cpu().numpy()
+        s = None if sigma is None else sigma.cpu().numpy()
+        return cp.eng.extract_offline(xn, None, m, s, out=on)
+
+    def step():
+        cp.corpus.extract_corpus(K5_SESSIONS, cp.day_of, cp.baseline, lambda s: xn, extract, cp.accumulate, n_channels=cp.C, device=cp.local)
+
+    cp.eng.extract_offline(xn, None, None, None, out=on)     # staging buffers, plan
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / steps
+    t = torch.tensor([dt], dtype=torch.float64, device=cp.dev)
+    if cp.world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    n_ext = len(cp.mine) + sum(1 for s in cp.baseline if s in cp.mine)
+    del xh, oh
+    return float(t.item()), n_ext * cp.T * cp.C * 8, n_ext * cp.eng.num_frames(cp.T) * cp.C * 8
+
+
+def raw_int16_e2e(torch, eng, x, mu_h, sg_h, n_calls, dist, world, barrier):
+    """hga_extract_offline_raw_host on int16 amplifier counts + per-channel gain (BCI2000MatFile.signals() formed on the
+    device): a quarter of the upload bytes.  Side entry: the input differs from the headline's."""
+    from delayed_speech_synthesis_b200 import transforms as TR
+    T, C = x.shape
+    gain_h = np.linspace(0.05, 0.15, C)
+    counts = torch.clamp(torch.round(x / torch.from_numpy(gain_h).to(x.device)), -32000, 32000).to(torch.int16)
+    ch = torch.empty((T, C), dtype=torch.int16, pin_memory=True)
+    ch.copy_(counts)
+    oh = torch.empty((eng.num_frames(T), C), dtype=torch.float64, pin_memory=True)
+    ident = TR.ChannelMap(TR.ChannelMapSpec.identity(C), eng.device)
+    cn, on = ch.numpy(), oh.numpy()
+    eng.extract_offline_raw(cn, ident, gain_h, None, mu_h, sg_h, out=on)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(n_calls):
+        eng.extract_offline_raw(cn, ident, gain_h, None, mu_h, sg_h, out=on)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / n_calls
+    t = torch.tensor([dt], dtype=torch.float64, device=x.device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    want = eng.extract_offline(ident.apply_raw(counts, gain_h), None, torch.from_numpy(mu_h).to(x.device), torch.from_numpy(sg_h).to(x.device))
+    ok = bool(torch.equal(oh.to(x.device), want))
+    del ch, oh, counts, want
+    return {"value": world * C * T / float(t.item()), "unit": UNIT, "ms_per_recording": 1e3 * float(t.item()), "h2d_bytes_per_recording": int(T * C * 2),
+            "matches_device_result": ok,
+            "path": "hga_extract_offline_raw_host: int16 counts x float64 gain expanded on the device (k_rawscale<int16, gain>), one recording per rank"}
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def run_single(args):
     import torch
-    import torch.distributed as dist
 
     from delayed_speech_synthesis_b200 import _lib
     from delayed_speech_synthesis_b200.engine import HgaEngine
-    from delayed_speech_synthesis_b200.ops import ChannelStats
-    from delayed_speech_synthesis_b200 import corpus
 
-    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the HGA path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     fs, C, secs = WORKLOADS[args.workload]
     T = fs * secs
     hbm_peak, peak_src = peaks()
+    placement = bind_near_gpu(torch, local)
 
-    # synthetic recording, generated on the device (Philox), distinct per rank
-    g = torch.Generator(device=dev)
-    g.manual_seed(20241104 + rank)
-    x = torch.empty((T, C), dtype=torch.float64, device=dev)
-    step_rows = max(1, (1 << 27) // C)
-    for r0 in range(0, T, step_rows):
-        x[r0:r0 + step_rows].normal_(generator=g)
-    x += (5.0 * torch.sin(2 * torch.pi * 120.0 * torch.arange(T, device=dev, dtype=torch.float64) / fs)).unsqueeze(1)
-
+    x = make_recording(torch, dev, T, C, fs, 20241104)
     eng = HgaEngine(fs, C, precision=args.precision, device=local)
-    # day baseline from the first 60 s of every rank's recording, combined over ranks
-    base = eng.extract_offline(x[: 60 * fs])
-    st = ChannelStats(C, local).update(base)
-    if world > 1:  # first collective of the process group (communicator set-up) stays outside the timed exchange
-        corpus.gather_accumulators(st.acc)
-        torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    acc = corpus.gather_accumulators(st.acc) if world > 1 else st.acc.unsqueeze(0)
-    merged = ChannelStats(C, local).merge(acc)
-    mu, sigma = merged.finalize(as_numpy=False)
-    torch.cuda.synchronize()
-    stats_ms = 1e3 * (time.perf_counter() - t0)
-
+    base = eng.extract_offline(x[: 60 * fs])                    # day baseline from the first 60 s
+    mu, sigma = base.mean(0), base.std(0, unbiased=False)
     F = eng.num_frames(T)
     out = torch.empty((F, C), dtype=torch.float64, device=dev)
 
     def step():
         eng.extract_offline(x, None, mu, sigma, out=out)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     for _ in range(max(args.warmup, 3)):
         step()
-    barrier()
-    # dominant-kernel time: CUDA events recorded by the library on the launching stream around the kernel itself
+    torch.cuda.synchronize()
+    # launch-sequence time (main kernel + carry fix-up): CUDA events recorded by the library on the launching stream
     eng.set_timing(True)
     kms = []
     for _ in range(min(args.steps, 10)):
@@ -285,29 +568,35 @@ def run_b200(args):
         kms.append(eng.last_kernel_ms())
     eng.set_timing(False)
     kernel_ms = float(np.median(kms))
-    barrier()
     l0 = lib.hga_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
-        barrier()
-        e0.record()
-        for _ in range(args.steps):
-            step()
-        e1.record()
-        barrier()
+        ms = time_steps(torch, step, args.steps, 0)
     launches = lib.hga_launch_count() - l0
-    ms = e0.elapsed_time(e1) / args.steps
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = world * C * T / (ms / 1e3)
+    value = C * T / (ms / 1e3)
+    plan = eng.last_plan()
+    achieved, frac, bytes_per = roofline_entry(C, T, eng.hop, kernel_ms, hbm_peak)
 
-    # ---- end to end through the host-buffer C-ABI call: pinned host input, host output, copies inside the timed region
+    # ---- the other precisions on the same resident input (same timing rules)
+    other = {}
+    for prec in ("f64", "f32", "mixed"):
+        if prec == args.precision:
+            continue
+        try:
+            e2 = HgaEngine(fs, C, precision=prec, device=local)
+            ms2, o2 = device_rate(torch, e2, x, mu, sigma, args.steps)
+            other[prec] = {"value": C * T / (ms2 / 1e3), "ms_per_step": ms2, "roofline_frac": roofline_entry(C, T, e2.hop, ms2, hbm_peak)[1],
+                           "max_abs_diff_vs_headline": float((o2 - out).abs().max().item()), "tolerance": TOLERANCE[prec], "plan": e2.last_plan(),
+                           "ncu": profile_facts(prec)}
+            del e2, o2
+        except Exception as exc:
+            other[prec] = {"error": repr(exc)}
+
+    # ---- end to end through the host-buffer C-ABI call: host input, host output, copies inside the timed region
     e2e = None
     try:
         if args.no_e2e:
-            raise RuntimeError('skipped (--no-e2e)')
+            raise RuntimeError("skipped (--no-e2e)")
+        h2d = h2d_bandwidth(torch, dev)
         xh = torch.empty((T, C), dtype=torch.float64, pin_memory=True)
         xh.copy_(x)
         oh = torch.empty((F, C), dtype=torch.float64, pin_memory=True)
@@ -315,122 +604,170 @@ def run_b200(args):
         xn, on = xh.numpy(), oh.numpy()
         n_e2e = max(2, min(args.steps, 5))
         eng.extract_offline(xn, None, mu_h, sg_h, out=on)
-        barrier()
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(n_e2e):
             eng.extract_offline(xn, None, mu_h, sg_h, out=on)
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / n_e2e
-        if world > 1:
-            t = torch.tensor([dt], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
-        e2e_ok = bool(torch.equal(oh.to(dev), out))
-        e2e = {"value": world * C * T / dt, "unit": UNIT, "h2d_bytes_per_step": int(T * C * 8), "d2h_bytes_per_step": int(F * C * 8),
-               "ms_per_step": 1e3 * dt, "matches_device_result": e2e_ok}
-        del xh
-        # side line: the same call fed with int16 amplifier counts + per-channel gain (BCI2000MatFile.signals() formed on
-        # the device, hga_extract_offline_raw_host): a quarter of the upload bytes.  Not the headline: the input differs.
-        if world == 1:
-            try:
-                from delayed_speech_synthesis_b200 import transforms as TR
-                gain_h = np.linspace(0.05, 0.15, C)
-                counts = torch.clamp(torch.round(x / torch.from_numpy(gain_h).to(dev)), -32000, 32000).to(torch.int16)
-                ch = torch.empty((T, C), dtype=torch.int16, pin_memory=True)
-                ch.copy_(counts)
-                ident = TR.ChannelMap(TR.ChannelMapSpec.identity(C), eng.device)
-                cn = ch.numpy()
-                eng.extract_offline_raw(cn, ident, gain_h, None, mu_h, sg_h, out=on)
-                t0 = time.perf_counter()
-                for _ in range(n_e2e):
-                    eng.extract_offline_raw(cn, ident, gain_h, None, mu_h, sg_h, out=on)
-                torch.cuda.synchronize()
-                dtr = (time.perf_counter() - t0) / n_e2e
-                want = eng.extract_offline(ident.apply_raw(counts, gain_h), None, mu, sigma)
-                e2e["raw_int16"] = {"value": C * T / dtr, "unit": UNIT, "ms_per_step": 1e3 * dtr, "h2d_bytes_per_step": int(T * C * 2),
-                                    "d2h_bytes_per_step": int(F * C * 8), "matches_device_result": bool(torch.equal(oh.to(dev), want)),
-                                    "path": "hga_extract_offline_raw_host: int16 counts x float64 gain expanded on the device (k_chanmap<int16, gain>)"}
-                del ch, counts, want
-            except Exception as exc:
-                e2e["raw_int16"] = {"error": repr(exc)}
+        e2e = {"value": C * T / dt, "unit": UNIT, "h2d_bytes_per_step": int(T * C * 8), "d2h_bytes_per_step": int(F * C * 8),
+               "ms_per_step": 1e3 * dt, "matches_device_result": bool(torch.equal(oh.to(dev), out)), "host_buffers": "page-locked (read by the DMA engine where they lie)",
+               "h2d_gbs_bare_copy": h2d, "placement": placement}
+        # pageable buffers (what BCI2000MatFile.signals() hands over): staged through the library's pinned ping-pong buffers
+        xp = np.empty((T, C), dtype=np.float64)
+        xp[:] = xn
+        op = np.empty((F, C), dtype=np.float64)
+        eng.extract_offline(xp, None, mu_h, sg_h, out=op)
+        t0 = time.perf_counter()
+        for _ in range(2):
+            eng.extract_offline(xp, None, mu_h, sg_h, out=op)
+        dtp = (time.perf_counter() - t0) / 2
+        e2e["pageable"] = {"value": C * T / dtp, "ms_per_step": 1e3 * dtp, "matches_device_result": bool(np.array_equal(op, on)),
+                           "path": "pageable numpy in / out: host copies into two 64 MB pinned staging buffers overlap the DMA"}
+        del xp, op, xh
+        try:
+            e2e["raw_int16"] = raw_int16_e2e(torch, eng, x, mu_h, sg_h, n_e2e, None, 1, torch.cuda.synchronize)
+        except Exception as exc:
+            e2e["raw_int16"] = {"error": repr(exc)}
         del oh
     except Exception as exc:  # report, do not hide
         e2e = {"value": None, "unit": UNIT, "error": repr(exc)}
 
-    # ---- the other offline precision on the same resident input (reported beside the headline, same timing rules)
-    other = {}
-    for prec in ("f64", "f32"):
-        if prec == args.precision:
-            continue
-        try:
-            e2 = HgaEngine(fs, C, precision=prec, device=local)
-            o2 = torch.empty_like(out)
-            for _ in range(3):
-                e2.extract_offline(x, None, mu, sigma, out=o2)
-            barrier()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            for _ in range(args.steps):
-                e2.extract_offline(x, None, mu, sigma, out=o2)
-            a1.record()
-            barrier()
-            ms2 = a0.elapsed_time(a1) / args.steps
-            if world > 1:
-                t = torch.tensor([ms2], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                ms2 = float(t.item())
-            other[prec] = {"value": world * C * T / (ms2 / 1e3), "ms_per_step": ms2,
-                           "max_abs_diff_vs_headline": float((o2 - out).abs().max().item()), "warmup_samples": e2.warmup}
-            del e2, o2
-        except Exception as exc:
-            other[prec] = {"error": repr(exc)}
-
-    # ---- streaming (BASELINE config 3): 10-sample x C packets through the host-buffer C-ABI call, carried state
+    # ---- streaming (BASELINE config 3): 10-sample x C packets on one long-lived handle
     stream = None
-    if rank == 0 and world == 1 and not args.no_stream:
+    if not args.no_stream:
         try:
             stream = stream_latency(fs, C, mu.cpu().numpy(), sigma.cpu().numpy(), local)
         except Exception as exc:
             stream = {"error": repr(exc)}
+    del x, out
+    torch.cuda.empty_cache()
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    hop = eng.hop
-    bytes_per = 8.0 + 8.0 / hop
-    achieved = C * T * bytes_per / (kernel_ms / 1e3) / 1e9  # per rank: one launch per step
+    # ---- other BASELINE configurations on this GPU: short recordings (the chunking's worst case), k4, the k5 corpus
+    sides = {}
+    if not args.no_sides:
+        for name, precs, st in (("k1", ("f32", "f64"), 20), ("m10", ("f32", "f64"), 20), ("k4", ("f32", "f64"), 10)):
+            try:
+                sides[name] = side_workload(torch, dev, local, name, precs, st, hbm_peak)
+            except Exception as exc:
+                sides[name] = {"error": repr(exc)}
+        try:
+            cp = Corpus(torch, dev, local, 0, 1, args.precision)
+            ms5, exch = corpus_timed(torch, cp, 3, 1, torch.cuda.synchronize)
+            ok5, det5 = cp.parity(None)
+            sides["k5"] = {"workload": k5_name(), "value": cp.units / (ms5 / 1e3), "ms_per_step": ms5, "stats_exchange_ms": exch, "parity_ok": ok5, "parity": det5,
+                           "resident_recordings": cp.n_buf, "note": "64 sessions on one GPU read 32 resident recordings twice (236 GB of input, 180 GB of HBM)"}
+            del cp
+        except Exception as exc:
+            sides["k5"] = {"error": repr(exc)}
+        torch.cuda.empty_cache()
+
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        v, kind, sample = reference_rate(fs, C, 60, 1, budget_s=12.0)
-        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample}
-    traffic = None
-    tp = ROOT / "profiles" / "traffic.json"
-    if tp.exists():
-        traffic = json.loads(tp.read_text()).get(args.workload)
-        if isinstance(traffic, dict):
-            traffic = traffic.get(args.precision)
+    if not args.no_cpu_baseline:
+        cores = _host_cores()
+        v1, kind, _ = reference_rate(fs, C, 60, 1, steps=3)                    # the composition as the reference runs it: one process
+        vn, _, _ = reference_rate(fs, C, 600, cores, steps=2)                  # channels split over all host cores, 10 min sample
+        cpu = {"value": vn, "unit": UNIT, "cores": min(cores, C), "kind": kind,
+               "sample": f"{C} ch x 600 s @ {fs} Hz white float64, channels split over {min(cores, C)} processes that hold their block, median of 2 passes",
+               "one_core": {"value": v1, "sample": f"{C} ch x 60 s, one process, median of 3"}}
+    facts = profile_facts(args.precision)
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
         "data": "synthetic",
-        "config": {"workload": workload_name(args.workload), "precision": args.precision, "warmup_samples": eng.warmup,
-                   "l2": (f"input {T * C * 8 / 1e9:.2f} GB per step > 126 MB L2 (no flush needed)" if args.workload != "k1"
-                          else "k1 input (61 MB) fits L2: not a valid bench workload, parity-size only"),
-                   "sessions_per_rank": 1, "stats_exchange_ms": stats_ms},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                     "traffic": traffic, "peak_source": peak_src, "bytes_per_channel_sample": bytes_per,
-                     "kernel": "k_hga_pipe2 (section-pipelined cascade + framing + log + z-score)", "kernel_ms": kernel_ms,
-                     "binding_pipe": "fp64" if args.precision == "f64" else "fma (f32x2)"},
+        "config": {"workload": workload_name(args.workload), "precision": args.precision, "tolerance": TOLERANCE[args.precision],
+                   "l2": f"input {T * C * 8 / 1e9:.2f} GB per step > 126 MB L2 (no flush needed)", "plan": plan},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": frac,
+                     "traffic": (facts or {}).get("traffic_bytes_per_step"), "peak_source": peak_src, "bytes_per_channel_sample": bytes_per,
+                     "kernel": "k_hga_lanes (+ k_lane_fix, k_lane_fix_frames: the carried heads); kernel_ms is the whole launch sequence of a step",
+                     "kernel_ms": kernel_ms, "binding_pipe": "fp64" if args.precision == "f64" else "fma (packed f32x2)",
+                     "pipe_frac": (facts or {}).get("pipe_frac"), "ncu": facts},
         "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
-        "other_precisions": {k: dict(v, roofline_frac=(C * T * bytes_per / (v["ms_per_step"] / 1e3) / 1e9 / hbm_peak)
-                                      if "ms_per_step" in v else None) for k, v in other.items()},
-        "tolerance": {"f64": "max-abs 1e-9 per feature vs float64 oracle", "f32": "max-abs 1e-4 per feature vs float64 oracle"},
-        "stream_latency": stream,
+        "other_precisions": other, "tolerance": TOLERANCE, "sides": sides, "stream_latency": stream,
     }
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+
+
+def run_corpus(args):
+    import torch
+    import torch.distributed as dist
+
+    from delayed_speech_synthesis_b200 import _lib
+
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the HGA path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    hbm_peak, peak_src = peaks()
+    placement = bind_near_gpu(torch, local)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    cp = Corpus(torch, dev, local, rank, world, args.precision)
+    cp.step()                                   # plans, scratch, the communicator's first collective
+    parity_ok, parity = cp.parity(dist)
+    barrier()
+    l0 = lib.hga_launch_count()
+    with ClockSampler(local) as clk:
+        ms, exch = corpus_timed(torch, cp, args.steps, max(args.warmup, 3), barrier)
+    launches = lib.hga_launch_count() - l0
+    t = torch.tensor([ms, exch or 0.0], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, exch = float(t[0].item()), float(t[1].item())
+    value = cp.units / (ms / 1e3)
+    # per-rank kernel view: one session's launch sequence
+    cp.eng.set_timing(True)
+    kms = []
+    for _ in range(5):
+        cp.extract(cp.buffers[0], None, None)
+        kms.append(cp.eng.last_kernel_ms())
+    cp.eng.set_timing(False)
+    kernel_ms = float(np.median(kms))
+    achieved, frac, bytes_per = roofline_entry(cp.C, cp.T, cp.eng.hop, kernel_ms, hbm_peak)
+
+    e2e = None
+    try:
+        if args.no_e2e:
+            raise RuntimeError("skipped (--no-e2e)")
+        h2d = h2d_bandwidth(torch, dev, barrier)
+        hb = torch.tensor([h2d], dtype=torch.float64, device=dev)
+        allh = [torch.empty_like(hb) for _ in range(world)]
+        dist.all_gather(allh, hb)
+        dt, up, down = corpus_e2e(torch, cp, dist, 2, barrier)
+        e2e = {"value": cp.units / dt, "unit": UNIT, "h2d_bytes_per_step": int(up), "d2h_bytes_per_step": int(down), "ms_per_step": 1e3 * dt,
+               "host_buffers": "page-locked, one recording per rank standing for each of its sessions",
+               "h2d_gbs_bare_copy_per_rank_all_ranks_at_once": [float(a.item()) for a in allh], "placement": placement,
+               "limiter": "host -> device copies: compare ms_per_step with h2d_bytes_per_step / the bare-copy rate measured with all ranks copying at once"}
+        try:
+            mu0 = np.full(cp.C, 3.0)
+            e2e["raw_int16"] = raw_int16_e2e(torch, cp.eng, cp.buffers[0], mu0, np.full(cp.C, 0.4), 3, dist, world, barrier)
+        except Exception as exc:
+            e2e["raw_int16"] = {"error": repr(exc)}
+    except Exception as exc:
+        e2e = {"value": None, "unit": UNIT, "error": repr(exc)}
+
+    if rank == 0:
+        facts = profile_facts(args.precision)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": k5_name(), "precision": args.precision, "tolerance": TOLERANCE[args.precision], "sessions_per_rank": len(cp.mine),
+                       "resident_recordings_per_rank": cp.n_buf, "l2": "every session is 3.69 GB > 126 MB L2 (no flush needed)",
+                       "timed_region": "per-day baseline extraction + statistics, NCCL all-gather of all days' (n, mean, M2), fixed-order merge, extraction + z-score of every owned session",
+                       "stats_exchange_ms": exch, "plan": cp.eng.last_plan()},
+            "parity_ok": parity_ok, "parity": parity,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": frac, "traffic": (facts or {}).get("traffic_bytes_per_step"),
+                         "peak_source": peak_src, "bytes_per_channel_sample": bytes_per, "kernel_ms": kernel_ms,
+                         "kernel": "per rank, one session: k_hga_lanes + carried-head fix-up", "pipe_frac": (facts or {}).get("pipe_frac")},
+            "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(), "tolerance": TOLERANCE,
+        }
+        print(json.dumps(line))
+    dist.destroy_process_group()
 
 
 def main():
@@ -440,15 +777,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="k2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="f64", choices=["f64", "f32", "exact"])
+    ap.add_argument("--precision", default="f32", choices=["f64", "f32", "mixed"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-stream", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sides", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        run_corpus(args)
     else:
-        run_b200(args)
+        run_single(args)
 
 
 if __name__ == "__main__":
