@@ -12,6 +12,22 @@ def shard_sessions(n_sessions: int, rank: int, world: int) -> List[int]:
     return list(range(rank, n_sessions, world))
 
 
+def shard_weighted(weights, rank: int, world: int) -> List[int]:
+    """Session indices of `rank` when session s costs weights[s]: heaviest first, each to the least loaded rank (ties to the
+    lowest rank, equal weights in index order) — the same table on every rank.  A day's baseline session is extracted twice
+    (once raw for the statistics, once z-scored: prepare_corpus.py:190-199 then :209-227), so it weighs 2."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world {world}")
+    load = [0.0] * world
+    mine: List[int] = []
+    for s in sorted(range(len(weights)), key=lambda i: (-float(weights[i]), i)):
+        r = min(range(world), key=lambda k: (load[k], k))
+        load[r] += float(weights[s])
+        if r == rank:
+            mine.append(s)
+    return sorted(mine)
+
+
 def gather_accumulators(acc, group=None):
     """All-gather a (k, 3, C) or (3, C) block of (n, mean, M2) accumulators -> (world * k, 3, C), rank-major.
 
@@ -85,8 +101,8 @@ def extract_corpus(n_sessions: int, day_of, baseline_sessions, get_session, extr
     """The reference's corpus build (prepare_corpus.py:179-236) over the ranks of a process group, one process per GPU:
 
       1. `ZScoresFromSyllableRepetitions` (:183-199): per day, (n, mean, M2) of the features of that day's baseline
-         session(s); every rank does this for the baseline sessions it owns (sessions are dealt round-robin,
-         `shard_sessions`), days it owns nothing of stay (0, 0, 0);
+         session(s); every rank does this for the baseline sessions it owns (sessions are dealt by cost,
+         `shard_weighted`: a baseline session is extracted twice), days it owns nothing of stay (0, 0, 0);
       2. ONE exchange: all days' accumulators in one all-gather (3 * C float64 per day and rank; NCCL over NVLink on CUDA
          tensors), then the same fixed-order merge on every rank (`merge_days`) -> bit-identical (mu, sigma) everywhere;
       3. the main loop (:209-234): every owned session extracted and z-scored with its day's (mu, sigma) (:226-227).
@@ -104,8 +120,8 @@ def extract_corpus(n_sessions: int, day_of, baseline_sessions, get_session, extr
     rank = dist.get_rank(group) if world > 1 else 0
     slots = day_slots([day_of[s] for s in range(n_sessions)])
     n_days = len(slots)
-    mine = shard_sessions(n_sessions, rank, world)
     base = set(int(b) for b in baseline_sessions)
+    mine = shard_weighted([2 if s in base else 1 for s in range(n_sessions)], rank, world)
     acc = None
     for s in mine:
         if s in base:

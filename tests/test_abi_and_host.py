@@ -121,7 +121,12 @@ def test_ezmsg_standin_and_unit_declaration():
 
 
 def test_session_sharding():
-    from delayed_speech_synthesis_b200.corpus import day_slots, shard_sessions
+    from delayed_speech_synthesis_b200.corpus import day_slots, shard_sessions, shard_weighted
+    w = [2 if s % 8 == 0 else 1 for s in range(64)]        # k5: the first session of a day is its baseline (extracted twice)
+    for world in (1, 2, 4, 8):
+        parts = [shard_weighted(w, r, world) for r in range(world)]
+        assert sorted(s for p in parts for s in p) == list(range(64))
+        assert {sum(w[s] for s in p) for p in parts} == {72 // world}
     for world in (1, 2, 4, 8):
         got = sorted(s for r in range(world) for s in shard_sessions(64, r, world))
         assert got == list(range(64))

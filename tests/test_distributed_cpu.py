@@ -97,7 +97,7 @@ def _corpus_worker(rank, world, port, q):
     got = {}
     mu, sigma, slots = corpus.extract_corpus(len(sess), day_of, baseline, lambda s: sess[s], extract, accumulate, n_channels=C,
                                              on_features=lambda s, f: got.__setitem__(s, f.numpy().copy()))
-    assert sorted(got) == corpus.shard_sessions(len(sess), rank, world)
+    assert sorted(got) == corpus.shard_weighted([2 if s in baseline else 1 for s in range(len(sess))], rank, world)
     q.put((rank, mu.numpy().copy(), sigma.numpy().copy(), got))
     dist.barrier()
     dist.destroy_process_group()
