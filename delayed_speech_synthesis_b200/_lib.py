@@ -71,6 +71,7 @@ SIGNATURES = {
     "hga_launch_count": (_i64, []),
     "hga_set_timing": (C.c_int, [_vp, _i32]),
     "hga_last_kernel_ms": (_dbl, [_vp]),
+    "hga_last_kernel_split_ms": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 
 _lib = None

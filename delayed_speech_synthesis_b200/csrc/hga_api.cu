@@ -277,7 +277,8 @@ struct hga_handle {
   std::vector<double> mu_cache, sig_cache;
   bool musig_valid = false;
   cudaStream_t s_own = nullptr, s_copy = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_main = nullptr;
+  bool timed_main = false;
   std::vector<cudaEvent_t> slab_ev;
   int timing = 0;
   bool timed = false;
@@ -364,6 +365,7 @@ extern "C" int hga_create(const hga_config* cfg, hga_handle** out) {
   cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking);
   cudaEventCreate(&h->ev0);
   cudaEventCreate(&h->ev1);
+  cudaEventCreate(&h->ev_main);
   if ((rc = tile_zi(h, h->s_own))) { hga_destroy(h); return rc; }
   *out = h;
   return HGA_OK;
@@ -387,6 +389,7 @@ extern "C" int hga_destroy(hga_handle* h) {
   for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->ev_main) cudaEventDestroy(h->ev_main);
   if (h->s_own) cudaStreamDestroy(h->s_own);
   if (h->s_copy) cudaStreamDestroy(h->s_copy);
   delete h;
@@ -413,6 +416,7 @@ extern "C" int hga_set_timing(hga_handle* h, int32_t enable) {
   if (!h) return fail(HGA_ERR_INVALID, "null handle");
   h->timing = enable;
   h->timed = false;
+  h->timed_main = false;
   return HGA_OK;
 }
 extern "C" double hga_last_kernel_ms(hga_handle* h) {
@@ -423,6 +427,18 @@ extern "C" double hga_last_kernel_ms(hga_handle* h) {
     return -1.0;
   }
   return ms;
+}
+extern "C" int hga_last_kernel_split_ms(hga_handle* h, double* main_ms, double* rest_ms) {
+  if (!h) return fail(HGA_ERR_INVALID, "null handle");
+  if (!h->timed || !h->timed_main) return fail(HGA_ERR_INVALID, "no timed lane extraction on this handle (hga_set_timing, then a device extraction)");
+  float a = 0, b = 0;
+  if (cudaEventSynchronize(h->ev1) != cudaSuccess || cudaEventElapsedTime(&a, h->ev0, h->ev_main) != cudaSuccess ||
+      cudaEventElapsedTime(&b, h->ev_main, h->ev1) != cudaSuccess) {
+    return fail(HGA_ERR_CUDA, "event query failed: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  if (main_ms) *main_ms = a;
+  if (rest_ms) *rest_ms = b;
+  return HGA_OK;
 }
 extern "C" int64_t hga_num_frames(const hga_handle* h, int64_t rows) {
   if (!h || rows < h->cfg.frame_len) return 0;
@@ -616,9 +632,11 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
     if ((rc = lane_prepare(h, n_seg, seg_start, seg_len, out_row, xlo, st))) return rc;
     CUtensorMap tm;
     if ((rc = lane_tensor(h, x, ldx, xlo, xhi, &tm))) return rc;
-    if (h->timing) CU(cudaEventRecord(h->ev0, st));
-    if ((rc = lane_launch(h->cfg.precision, hop, h->lk, h->lane_plan_host, lane_dev(h), tm, C, mu, sigma, out, ldo, h->n_sm, st))) return rc;
-    if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; }
+    LaneDev ld = lane_dev(h);
+    h->timed_main = false;
+    if (h->timing) { CU(cudaEventRecord(h->ev0, st)); ld.ev_main = h->ev_main; }
+    if ((rc = lane_launch(h->cfg.precision, hop, h->lk, h->lane_plan_host, ld, tm, C, mu, sigma, out, ldo, h->n_sm, st))) return rc;
+    if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; h->timed_main = true; }
     return HGA_OK;
   }
   if (variant == 0) {

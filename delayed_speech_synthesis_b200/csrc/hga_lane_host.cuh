@@ -362,6 +362,7 @@ struct LaneDev {  // device copies of a LanePlan and the scratch it needs (owned
   // caller's and n_items counts its entries; the fix-up kernels run once, after the last part
   int n_items = -1;       // -1: all items of the plan
   bool skip_fix = false;
+  cudaEvent_t ev_main = nullptr;  // when set: recorded right behind the main kernel (hga_last_kernel_split_ms)
 };
 
 typedef CUresult (*LaneEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -444,6 +445,7 @@ inline int lane_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d
   if (cudaMemsetAsync(d.counter, 0, sizeof(int), st) != cudaSuccess) return -1;
   const int grid = std::max(1, std::min(n_sm, (a.n_items + NW - 1) / NW));
   kern<<<grid, 32 * NW, SM::total, st>>>(k, a, tm);
+  if (d.ev_main) cudaEventRecord(d.ev_main, st);
   const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
   return cudaGetLastError() == cudaSuccess ? launches : -1;
 }
@@ -460,6 +462,7 @@ inline int lanes_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& 
   lane_fill_args(p, d, C, mu, sigma, out, ldo, prof, a);
   const int grid = std::max(1, std::min(n_sm, (a.n_items + NI - 1) / NI));
   kern<<<grid, 32 * NI * NS, SM::total, st>>>(k, a, tm);
+  if (d.ev_main) cudaEventRecord(d.ev_main, st);
   const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
   return cudaGetLastError() == cudaSuccess ? launches : -1;
 }

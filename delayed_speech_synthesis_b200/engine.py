@@ -126,6 +126,12 @@ class HgaEngine:
     def last_kernel_ms(self) -> float:
         return float(self._lib.hga_last_kernel_ms(self._h))
 
+    def last_kernel_split_ms(self):
+        """(dominant kernel alone, carry + fix-up kernels behind it) of the last timed device extraction, in ms."""
+        a, b = C.c_double(0), C.c_double(0)
+        check(self._lib.hga_last_kernel_split_ms(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     # -- offline ---------------------------------------------------------------------------------------------------
     def _segments(self, rows: int, segments):
         if segments is None:

@@ -231,10 +231,14 @@ int hga_extract_offline_raw_host(hga_handle* h, hga_chanmap* map, const void* x_
 /* ---- introspection for bench.py / tests ------------------------------------------------------------------------- */
 /* Kernel launches issued through this library by the calling process since load (all handles). */
 int64_t hga_launch_count(void);
-/* Device time (ms, CUDA events on the launching stream) of the dominant kernel of the last hga_extract_offline call
+/* Device time (ms, CUDA events on the launching stream) of the kernel sequence of the last hga_extract_offline call
  * on this handle when timing was enabled with hga_set_timing(h, 1); -1 if unavailable. */
 int hga_set_timing(hga_handle* h, int32_t enable);
 double hga_last_kernel_ms(hga_handle* h);
+/* The same time split at the end of the dominant kernel (k_hga_lanes / k_hga_lane): main_ms = that kernel alone,
+ * rest_ms = state carry + head fix-up + seam frames behind it.  HGA_ERR_INVALID when the last timed call did not
+ * take the lane kernels. */
+int hga_last_kernel_split_ms(hga_handle* h, double* main_ms, double* rest_ms);
 
 #ifdef __cplusplus
 }
