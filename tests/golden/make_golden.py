@@ -13,7 +13,9 @@ Pieces executed:
   * the reference's channel-transform classes (local/common.py), cut out of its AST and executed unmodified
     (`python tests/golden/make_golden.py transforms` regenerates only transforms.npz);
   * the reference's packet code (development_amplifier.py BCI2000Package, local/units.py ZMQConnector.interpret_bytes), cut
-    out of the AST and executed unmodified (`... make_golden.py packets` regenerates only packets.npz).
+    out of the AST and executed unmodified (`... make_golden.py packets` regenerates only packets.npz);
+  * the reference's Experiment classes (local/common.py:676-880: trial / stimulus indices from StimulusCode), cut out of the
+    AST and executed unmodified on synthetic state vectors (`... make_golden.py trials` regenerates only trials.npz).
 """
 from __future__ import annotations
 
@@ -124,7 +126,82 @@ def packets_golden():
     np.savez(HERE / "packets.npz", **out)
 
 
+def trial_cases():
+    """Synthetic BCI2000 `StimulusCode` state vectors (the committed inputs of trials.npz): regular runs of both paradigms,
+    a recording that ends inside a stimulus, back-to-back non-zero codes, a single trial, leading / trailing rest."""
+    rng = np.random.Generator(np.random.Philox(key=[20241104, 5]))
+    cases = {}
+
+    def paradigm(n_trials, n_codes, lead, stim, speak, rest, jitter, tail, open_end=False, back_to_back=False):
+        parts, codes = [np.zeros(lead, np.int16)], rng.integers(1, n_codes + 1, n_trials)
+        for i, cde in enumerate(codes):
+            parts.append(np.full(stim + int(rng.integers(0, jitter + 1)), cde, np.int16))
+            if back_to_back and i % 3 == 1:
+                parts.append(np.full(stim // 2, (cde % n_codes) + 1, np.int16))
+            parts.append(np.zeros(speak + int(rng.integers(0, jitter + 1)) + rest, np.int16))
+        if open_end:
+            parts.append(np.full(stim // 2, codes[0], np.int16))
+        else:
+            parts.append(np.zeros(tail, np.int16))
+        return np.concatenate(parts)
+
+    cases["syll_regular"] = ("SyllableRepetition", paradigm(24, 12, 3000, 700, 1800, 0, 0, 4000), 12)
+    cases["syll_jitter"] = ("SyllableRepetition", paradigm(40, 12, 1234, 650, 1500, 0, 300, 2500), 12)
+    cases["syll_two_trials"] = ("SyllableRepetition", paradigm(2, 4, 100, 50, 120, 0, 0, 500), 4)
+    cases["syll_short_tail"] = ("SyllableRepetition", paradigm(6, 6, 500, 400, 900, 0, 50, 10), 6)
+    cases["key_regular"] = ("KeywordReading", paradigm(30, 6, 2000, 2000, 1000, 500, 0, 3000), 6)
+    cases["key_jitter"] = ("KeywordReading", paradigm(50, 6, 10, 1500, 700, 200, 400, 1), 6)
+    cases["key_open_end"] = ("KeywordReading", paradigm(12, 6, 800, 1000, 600, 0, 100, 0, open_end=True), 6)
+    cases["key_back_to_back"] = ("KeywordSynthesis", paradigm(15, 6, 400, 900, 500, 0, 100, 700, back_to_back=True), 6)
+    cases["key_single"] = ("KeywordReading", paradigm(1, 6, 300, 500, 400, 0, 0, 200), 6)
+    cases["key_none"] = ("KeywordReading", np.zeros(5000, np.int16), 6)
+    return cases
+
+
+def trials_golden():
+    """The reference's Experiment classes (local/common.py:676-880), cut out of the AST and executed unmodified on the
+    synthetic state vectors above; BCI2000MatFile.trial_indices' min_trial_length clamp (:432-445) written out literally."""
+    import ast
+    from abc import ABC, abstractmethod
+    from functools import partial
+    from typing import Callable, Dict, List, Optional, Tuple, Union
+    src = Path("/root/reference/local/common.py").read_text()
+    want = ["Experiment", "SyllableRepetition", "KeywordReading", "ExperimentMapping"]
+    ns = {"np": np, "os": os, "ABC": ABC, "abstractmethod": abstractmethod, "Dict": Dict, "List": List, "Optional": Optional, "Tuple": Tuple,
+          "Union": Union, "Callable": Callable, "partial": partial}
+    for node in ast.parse(src).body:
+        if isinstance(node, ast.ClassDef) and node.name in want:
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "/root/reference/local/common.py", "exec"), ns)
+    out = {}
+    for name, (paradigm, code, n_codes) in trial_cases().items():
+        stimuli = [f"stim{j + 1:02d}" for j in range(n_codes)]
+        cls = ns["ExperimentMapping"].get_experiment_class(f"/data/day1/{paradigm}_Run01.mat")
+        exp = cls(code, stimuli)
+        out[f"{name}.paradigm"] = np.array(paradigm)
+        out[f"{name}.code"] = code
+        out[f"{name}.n_codes"] = np.array(n_codes)
+        for kind, fn in (("trials", exp.get_trial_indices), ("stimuli", exp.get_stimuli_indices)):
+            try:
+                res = fn()
+                out[f"{name}.{kind}.labels"] = np.array([r[0] for r in res], dtype="U16")
+                out[f"{name}.{kind}.bounds"] = np.array([[int(r[1]), int(r[2])] for r in res], dtype=np.int64).reshape(-1, 2)
+            except Exception as exc:   # the reference raises on degenerate vectors (e.g. IndexError without any trial)
+                out[f"{name}.{kind}.raises"] = np.array(type(exc).__name__)
+        try:
+            bl = exp.get_webfm_baseline_windows(1000)
+            out[f"{name}.baseline.bounds"] = np.array([[int(r[1]), int(r[2])] for r in bl], dtype=np.int64).reshape(-1, 2)
+            run = exp.get_experiment_run_indices()
+            out[f"{name}.run"] = np.array([int(run[1]), int(run[2])], dtype=np.int64)
+        except Exception as exc:
+            out[f"{name}.run.raises"] = np.array(type(exc).__name__)
+    np.savez_compressed(HERE / "trials.npz", **out)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "trials":
+        trials_golden()
+        print("golden written: trials.npz")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "packets":
         packets_golden()
         print("golden written: packets.npz")
