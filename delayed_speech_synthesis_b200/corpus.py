@@ -263,8 +263,8 @@ def _raw_supported(a):
 class BCI2000MatFile:
     """The accessors of the reference's `.mat` wrapper that feed this path (local/common.py:399-470): sampling rate, channel
     bookkeeping and the signal matrix.  `raw()` returns the two factors of `signals()` so that `extract_trials(..., gain=)`
-    can form the product on the device.  Trial / stimulus index extraction (the per-experiment `StimulusCode` state machines,
-    local/common.py:676-881) stays with the reference: its (label, start, stop) list is what `extract_trials` takes."""
+    can form the product on the device.  `trial_indices` / `stimuli_indices` (local/common.py:432-456) come from the
+    vectorised state-vector scans of `trials.py`; their (label, start, stop) list is what `extract_trials` takes."""
 
     def __init__(self, mat_filename: str):
         from scipy.io import loadmat
@@ -294,6 +294,14 @@ class BCI2000MatFile:
     def signals(self):
         signal, gain = self.raw()
         return signal * gain
+
+    def trial_indices(self, min_trial_length=None):
+        from . import trials
+        return trials.trial_indices(self.mat, self.mat_filename, self.fs, min_trial_length)
+
+    def stimuli_indices(self):
+        from . import trials
+        return trials.stimuli_indices(self.mat, self.mat_filename)
 
     def ordered_stimulus_codes(self):
         import numpy as np

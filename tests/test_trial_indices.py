@@ -86,3 +86,26 @@ def test_segment_table_is_the_reference_slicing():
     s3, l3, _, _ = TR.segment_table([("a", 900, 990)], fs, 1000, L, hop)
     assert (s3[0], l3[0]) == (900, 100)
     assert TR.segment_table([], fs, 1000, L, hop)[0].shape == (0,)
+
+
+def test_mat_wrapper_trial_indices(tmp_path):
+    """`BCI2000MatFile.trial_indices / stimuli_indices` (local/common.py:432-456) on a file with the reference's field layout."""
+    from scipy.io import savemat
+
+    from delayed_speech_synthesis_b200 import corpus
+
+    name = "key_regular"
+    code = GOLD[f"{name}.code"]
+    stimuli = [f"stim{j + 1:02d}" for j in range(int(GOLD[f"{name}.n_codes"]))]
+    cell = np.empty((2, len(stimuli)), dtype=object)
+    cell[0, :] = stimuli
+    cell[1, :] = "x"
+    path = tmp_path / "KeywordReading_Run07.mat"
+    savemat(path, {"signal": np.zeros((len(code), 2), np.int16),
+                   "parameters": {"SamplingRate": {"NumericValue": 1000}, "SourceChGain": {"NumericValue": np.ones(2)}, "Stimuli": {"Value": cell}},
+                   "states": {"StimulusCode": code.astype(np.uint8)}})
+    f = corpus.BCI2000MatFile(str(path))
+    _check(name, "trials", f.trial_indices())
+    _check(name, "stimuli", f.stimuli_indices())
+    long = f.trial_indices(min_trial_length=2.5)
+    assert all(b - a >= 2500 for _, a, b in long)

@@ -134,6 +134,7 @@ struct DevPlan {
   }
 };
 
+static double g_piece_ops = 14000.0;   // `fix` mode sweeps it
 static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, size_t ysize, DevPlan& dp, bool verbose, double tol = 1e-11) {
   dp.d.work = dp.up(p.work);
   dp.d.fix = dp.up(p.fix);
@@ -146,7 +147,7 @@ static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, s
   dp.d.E = (double*)dp.raw(p.fix.size() * kLaneState * CP * 8);
   dp.d.S0 = (double*)dp.raw(p.fix.size() * kLaneState * CP * 8);
   LaneFixPlan fp;
-  lane_build_fix(k, hop, fp);
+  lane_build_fix(k, hop, fp, g_piece_ops);
   dp.d.subs = dp.up(fp.subs);
   dp.d.n_sub = (int)fp.subs.size();
   dp.d.P = dp.up(fp.P);
@@ -361,6 +362,58 @@ int main(int argc, char** argv) {
       cudaFree(x);
       cudaFree(out);
     }
+  }
+  if (mode == "fix") {  // the fix-up kernels alone (after one full launch has filled the scratch), per piece size
+    const int fs = 1000, hop = 10, C = 128;
+    const Coefs co = load_coefs(fs, dir);
+    Cascade q;
+    build_cascade(co, q);
+    int64_t T = 3600000;
+    double *x, *out;
+    CK(cudaMalloc(&x, (size_t)T * C * 8));
+    CK(cudaMalloc(&out, (size_t)(T / hop) * C * 8));
+    k_fill<<<(unsigned)(((size_t)T * C + 255) / 256), 256>>>(x, T, C, C, fs);
+    CK(cudaDeviceSynchronize());
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int reps = 10;
+    for (double po : {14000.0, 10000.0, 7000.0, 20000.0, 28000.0}) {
+      g_piece_ops = po;
+#define FIX_X(V, TOL, NAME)                                                                          \
+  {                                                                                                  \
+    LaneConst k;                                                                                     \
+    lane_build_const(q, 5 * hop, hop, 0.01, TOL, k);                                                 \
+    LanePlan p;                                                                                      \
+    const int64_t s0 = 0, o0 = 0;                                                                    \
+    lane_plan(k, hop, C, 32 * V::Pol::CPL, 1, &s0, &T, &o0, 0, (int64_t)n_sm * V::workers_per_sm, true, p, 0); \
+    DevPlan dp;                                                                                      \
+    upload_plan(k, p, C, hop, sizeof(typename V::Pol::TY), dp, false, TOL);                          \
+    CUtensorMap tm;                                                                                  \
+    lane_tensor_map(encode_fn(), x, C, C, T, 32 * V::Pol::CPL, V::tb, &tm);                          \
+    V::template launch<false>(k, p, dp.d, tm, C, nullptr, nullptr, out, n_sm, nullptr);              \
+    CK(cudaDeviceSynchronize());                                                                     \
+    float sum = 0.f, best = 1e30f;                                                                   \
+    for (int i = 0; i < 12; ++i) {                                                                   \
+      CK(cudaEventRecord(e0));                                                                       \
+      lane_launch_fix<typename V::Pol::TY, 10>(k, p, dp.d, C, nullptr, nullptr, out, C, 0);          \
+      CK(cudaEventRecord(e1));                                                                       \
+      CK(cudaEventSynchronize(e1));                                                                  \
+      float ms;                                                                                      \
+      CK(cudaEventElapsedTime(&ms, e0, e1));                                                         \
+      if (i >= 2) { sum += ms; best = std::min(best, ms); }                                          \
+    }                                                                                                \
+    printf("%-14s piece_ops %-6.0f pieces %-3d fix-ups %-4zu blocks %-5zu  fix kernels mean %.4f ms best %.4f ms\n", NAME, po, dp.d.n_sub, p.fix.size(), \
+           p.fix.size() * dp.d.n_sub * ((p.groups * p.cw / (int)(8 / sizeof(typename V::Pol::TY)) + 63) / 64), sum / 10, best); \
+    dp.release();                                                                                    \
+  }
+      { using V_ = Staged<LaneF32, 10, 60, 2, 2, 2, 3, 5>; FIX_X(V_, 1e-6, "f32") }
+      { using V_ = Staged<LaneF64, 10, 80, 2, 2, 2, 3, 5>; FIX_X(V_, 1e-11, "f64") }
+    }
+    g_piece_ops = 14000.0;
+    { using V_ = Staged<LaneF32, 10, 60, 2, 2, 2, 3, 5>; TIME_X(V_, 1e-6, "f32 2-stage x2 TB60 (whole step)") }
+    { using V_ = Staged<LaneF64, 10, 80, 2, 2, 2, 3, 5>; TIME_X(V_, 1e-11, "f64 2-stage x2 TB80 (whole step)") }
+    { using V_ = OneStage<LaneMix, 10, 50, 4, 2, 5>; TIME_X(V_, 1e-7, "mix TB50 NW4 (whole step)") }
   }
   if (mode == "prof") {  // one variant, few launches: the target of an ncu run
     const int fs = 1000, hop = 10, C = 128;
