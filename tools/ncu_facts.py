@@ -107,7 +107,12 @@ def main():
         }
         fix = facts["_captures"].get(f"fix_{prec}")
         if fix:
-            entry["fixup_kernels"] = [{k: l[k] for k in ("kernel", "ms_under_ncu", "dram_read_bytes", "dram_write_bytes", "grid", "regs")} for l in fix["launches"]]
+            seen, rows = set(), []
+            for l in fix["launches"]:   # the first captured launch of each kernel
+                if l["kernel"] not in seen:
+                    seen.add(l["kernel"])
+                    rows.append({k: l[k] for k in ("kernel", "ms_under_ncu", "dram_read_bytes", "dram_write_bytes", "grid", "regs", "pipe_fma_pct_elapsed", "issue_active_pct")})
+            entry["fixup_kernels"] = rows
         facts[prec] = entry
     facts_path.write_text(json.dumps(facts, indent=1) + "\n")
     print(facts_path)
