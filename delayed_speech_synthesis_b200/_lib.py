@@ -71,6 +71,9 @@ SIGNATURES = {
     "hga_launch_count": (_i64, []),
     "hga_set_timing": (C.c_int, [_vp, _i32]),
     "hga_last_kernel_ms": (_dbl, [_vp]),
+    "hga_debug_guards": (C.c_int, [C.c_int32]),
+    "hga_debug_check_guards": (C.c_int64, []),
+    "hga_debug_guarded_buffers": (C.c_int64, []),
     "hga_last_kernel_split_ms": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 

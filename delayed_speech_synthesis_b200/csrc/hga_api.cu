@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -61,30 +62,79 @@ extern "C" int hga_device_count(void) {
 }
 
 // Growable device buffer.
+// Guard bands (test instrumentation, hga_debug_guards): when enabled, every device buffer the library allocates gets
+// kGuardBytes of a fill pattern in front of and behind the bytes asked for; hga_debug_check_guards reads them back.
+// compute-sanitizer is not available on every pool; an overrun of the library's own scratch shows up here instead.
+constexpr size_t kGuardBytes = 64 << 10;
+constexpr int kGuardFill = 0xA5;
+static std::atomic<int> g_guards{0};
+struct DevBuf;
+static std::mutex g_guard_mu;
+static std::vector<DevBuf*>& guard_registry() {
+  static std::vector<DevBuf*> r;
+  return r;
+}
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
+  void* base = nullptr;   // what cudaMalloc returned (== p without guard bands)
+  bool guarded = false;
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { unregister(); }
+  void unregister() {
+    if (!guarded) return;
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    auto& r = guard_registry();
+    r.erase(std::remove(r.begin(), r.end(), this), r.end());
+    guarded = false;
+  }
   int reserve(size_t bytes) {
     if (bytes <= cap) return HGA_OK;
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-    cudaError_t e = cudaMalloc(&p, bytes);
+    release();
+    const bool guard = g_guards.load(std::memory_order_relaxed) != 0;
+    const size_t total = bytes + (guard ? 2 * kGuardBytes : 0);
+    cudaError_t e = cudaMalloc(&base, total);
     if (e != cudaSuccess) {
       cudaGetLastError();
-      return fail(HGA_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+      base = nullptr;
+      return fail(HGA_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", total, cudaGetErrorString(e));
+    }
+    p = base;
+    if (guard) {
+      p = static_cast<char*>(base) + kGuardBytes;
+      cudaMemset(base, kGuardFill, kGuardBytes);
+      cudaMemset(static_cast<char*>(p) + bytes, kGuardFill, kGuardBytes);
+      std::lock_guard<std::mutex> lk(g_guard_mu);
+      guard_registry().push_back(this);
+      guarded = true;
     }
     cap = bytes;
     return HGA_OK;
   }
   void release() {
-    if (p) cudaFree(p);
-    p = nullptr;
+    unregister();
+    if (base) cudaFree(base);
+    base = p = nullptr;
     cap = 0;
   }
   template <class T>
   T* as() const { return static_cast<T*>(p); }
 };
+static void swap_bufs(DevBuf& a, DevBuf& b) {   // the registry keeps pointing at a and b: both stay registered or neither
+  std::swap(a.p, b.p);
+  std::swap(a.cap, b.cap);
+  std::swap(a.base, b.base);
+  if (a.guarded != b.guarded) {
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    auto& r = guard_registry();
+    DevBuf* was = a.guarded ? &a : &b;
+    DevBuf* now = a.guarded ? &b : &a;
+    std::replace(r.begin(), r.end(), was, now);
+    std::swap(a.guarded, b.guarded);
+  }
+}
 struct PinBuf {
   void* p = nullptr;
   size_t cap = 0;
@@ -428,6 +478,29 @@ extern "C" double hga_last_kernel_ms(hga_handle* h) {
   }
   return ms;
 }
+extern "C" int hga_debug_guards(int32_t enable) {
+  g_guards.store(enable ? 1 : 0, std::memory_order_relaxed);
+  return HGA_OK;
+}
+extern "C" int64_t hga_debug_check_guards(void) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return fail(HGA_ERR_CUDA, "synchronize failed: %s", cudaGetErrorString(cudaGetLastError()));
+  std::lock_guard<std::mutex> lk(g_guard_mu);
+  std::vector<unsigned char> host(kGuardBytes);
+  int64_t bad = 0;
+  for (DevBuf* b : guard_registry()) {
+    const char* bands[2] = {static_cast<const char*>(b->base), static_cast<const char*>(b->p) + b->cap};
+    for (const char* band : bands) {
+      if (cudaMemcpy(host.data(), band, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(HGA_ERR_CUDA, "guard read-back failed");
+      for (size_t i = 0; i < kGuardBytes; ++i)
+        if (host[i] != kGuardFill) { ++bad; break; }
+    }
+  }
+  return bad;   // number of overwritten guard bands
+}
+extern "C" int64_t hga_debug_guarded_buffers(void) {
+  std::lock_guard<std::mutex> lk(g_guard_mu);
+  return (int64_t)guard_registry().size();
+}
 extern "C" int hga_last_kernel_split_ms(hga_handle* h, double* main_ms, double* rest_ms) {
   if (!h) return fail(HGA_ERR_INVALID, "null handle");
   if (!h->timed || !h->timed_main) return fail(HGA_ERR_INVALID, "no timed lane extraction on this handle (hga_set_timing, then a device extraction)");
@@ -748,8 +821,8 @@ static int bulk_push(hga_handle* h, const double* x, int64_t n, int64_t ldx, con
     rc = extract_offline_dev(h, x, ldx, 1, &s0, &n, &o0, mu, sigma, out_shift, ldo, st, h->state2.as<double>(), h->framebuf2.as<double>(),
                              first ? nullptr : h->state.as<double>(), first ? nullptr : h->framebuf.as<double>(), /*allow_short=*/true);
     if (rc) return rc;
-    std::swap(h->state, h->state2);
-    std::swap(h->framebuf, h->framebuf2);
+    swap_bufs(h->state, h->state2);
+    swap_bufs(h->framebuf, h->framebuf2);
   } else {
     if ((rc = h->ybuf.reserve((size_t)(ov + n) * C * 8))) return rc;
     double* yb = h->ybuf.as<double>();

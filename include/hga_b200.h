@@ -240,6 +240,14 @@ double hga_last_kernel_ms(hga_handle* h);
  * take the lane kernels. */
 int hga_last_kernel_split_ms(hga_handle* h, double* main_ms, double* rest_ms);
 
+/* Test instrumentation (compute-sanitizer is not available on every pool): with guards enabled, every device buffer the
+ * library allocates from then on carries 64 KB of a fill pattern in front of and behind it.  hga_debug_check_guards
+ * synchronises the device and returns the number of guard bands that no longer hold the pattern (0 = no kernel wrote
+ * outside the library's own scratch), hga_debug_guarded_buffers how many buffers are being watched. */
+int hga_debug_guards(int32_t enable);
+int64_t hga_debug_check_guards(void);
+int64_t hga_debug_guarded_buffers(void);
+
 #ifdef __cplusplus
 }
 #endif
