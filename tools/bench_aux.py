@@ -64,7 +64,7 @@ mu_t, sg_t = torch.zeros(C, dtype=torch.float64, device="cuda"), torch.ones(C, d
 s = timed(lambda: ops.log_power(x, 1000, 0.05, 0.01), n=5, warm=2)      # includes the host-side window-index arithmetic of the call
 F = (T - 50) // 10 + 1
 gb = (T * C * 8 + F * C * 8) / s / 1e9
-out["compute_log_power_features (k_frames_roll; k_frames_seq with HGA_B200_FRAMES_ROLL=0; exact row-order sums) 3.6 M x 128"] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}
+out["compute_log_power_features (k_frames_roll, exact row-order sums) 3.6 M x 128"] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}
 s = timed(lambda: ops.zscore(f, mu_t, sg_t))
 gb = 2 * f.numel() * 8 / s / 1e9
 out["zscore 2.88 M x 128"] = {"ms": s * 1e3, "GB/s": gb, "frac_hbm": gb / peak}

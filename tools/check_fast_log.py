@@ -1,4 +1,4 @@
-"""NumPy emulation of the two device logs (csrc/hga_kernels_pipe.cuh fast_log, csrc/hga_kernels_pipe2.cuh tab_log):
+"""NumPy emulation of the device logs (csrc/hga_async.cuh tab_log, and the atanh-series fast_log it replaced):
 series degree / table / ln2 split check against numpy.log (long double)."""
 import numpy as np
 
