@@ -254,10 +254,20 @@ inline void lane_plan(const LaneConst& k, int hop, int C, int cw, int n_seg, con
       fix_ops += (double)(k.stage_rows[i] - r0) * ops;
       r0 = k.stage_rows[i];
     }
-    const double fix_cost = 2.5 * fix_ops / 56.0;
+    const double fix_cost = 2.0 * fix_ops / 56.0;   // measured: k_lane_fix costs twice its operation count (profiles/r02_ncu_fix_f32.csv)
     double best = 1e300;
     const int64_t min_Lc = std::max<int64_t>(16 * hop, 320);
-    for (int64_t n = 1; n <= (1 << 20); n = n < 64 ? n + 1 : n + n / 16) {
+    // candidate chunk counts: every n up to 64, then a geometric ladder, plus the counts that fill the workers exactly
+    // (n * groups == k * workers) — the ladder alone steps over them (141 -> 149 chunks around the 148 that fill 296 workers)
+    std::vector<int64_t> cand;
+    for (int64_t n = 1; n <= (1 << 20); n = n < 64 ? n + 1 : n + n / 16) cand.push_back(n);
+    for (int64_t kk = 1; kk <= 32; ++kk) {
+      const int64_t n = workers * kk / groups;
+      if (n >= 1) cand.push_back(n);
+    }
+    std::sort(cand.begin(), cand.end());
+    cand.erase(std::unique(cand.begin(), cand.end()), cand.end());
+    for (int64_t n : cand) {
       const int64_t Lc = ((maxT + n - 1) / n + hop - 1) / hop * hop;
       if (n > 1 && Lc < min_Lc) break;
       std::vector<int64_t> lens;
