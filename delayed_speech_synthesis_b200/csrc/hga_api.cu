@@ -324,6 +324,8 @@ struct hga_handle {
   cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   unsigned long long push_seq = 0;
   bool push_inflight = false;         // a host push returned on its completion slots; its kernel may still be storing state
+  cudaEvent_t dev_push_ev = nullptr;  // recorded on the caller's stream behind every device push (hga_stream_push)
+  bool dev_push_pending = false;      // ... and not yet waited for by the handle's own stream
   std::vector<double> mu_cache, sig_cache;
   bool musig_valid = false;
   cudaStream_t s_own = nullptr, s_copy = nullptr;
@@ -336,6 +338,14 @@ struct hga_handle {
 
 // Host pushes that poll completion slots return before their kernel has stored the new remainder / filter state on the
 // handle's own stream; anything that touches that state from another stream (or frees it) waits for it first.
+// The streaming state lives on the device and is updated by whichever stream the push ran on: a device push on the
+// caller's stream, host / packet pushes on s_own.  Work on s_own is ordered behind the last device push.
+static void order_after_dev_push(hga_handle* h) {
+  if (h->dev_push_pending) {
+    cudaStreamWaitEvent(h->s_own, h->dev_push_ev, 0);
+    h->dev_push_pending = false;
+  }
+}
 static void drain_push(hga_handle* h) {
   if (h->push_inflight) {
     cudaStreamSynchronize(h->s_own);
@@ -440,6 +450,7 @@ extern "C" int hga_destroy(hga_handle* h) {
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev_main) cudaEventDestroy(h->ev_main);
+  if (h->dev_push_ev) cudaEventDestroy(h->dev_push_ev);
   if (h->s_own) cudaStreamDestroy(h->s_own);
   if (h->s_copy) cudaStreamDestroy(h->s_copy);
   delete h;
@@ -910,7 +921,13 @@ extern "C" int hga_stream_push(hga_handle* h, const double* x_dev, int64_t n, in
   if (ldx < h->cfg.n_channels || ldo < h->cfg.n_channels) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
   CU(cudaSetDevice(h->cfg.device));
   drain_push(h);
-  return stream_push_dev(h, x_dev, n, ldx, mu_dev, sigma_dev, out_dev, ldo, n_frames, (cudaStream_t)stream);
+  const int rc = stream_push_dev(h, x_dev, n, ldx, mu_dev, sigma_dev, out_dev, ldo, n_frames, (cudaStream_t)stream);
+  if (rc == HGA_OK && (cudaStream_t)stream != h->s_own) {
+    if (!h->dev_push_ev) CU(cudaEventCreateWithFlags(&h->dev_push_ev, cudaEventDisableTiming));
+    CU(cudaEventRecord(h->dev_push_ev, (cudaStream_t)stream));
+    h->dev_push_pending = true;
+  }
+  return rc;
 }
 
 // mu/sigma host vectors are cached on the device; re-uploaded only when their contents change.
@@ -943,6 +960,7 @@ extern "C" int hga_stream_push_host(hga_handle* h, const double* x_host, int64_t
     return fail(HGA_ERR_INVALID, "push of %lld rows outside [1, max_push_rows]", (long long)n);
   CU(cudaSetDevice(h->cfg.device));
   cudaStream_t st = h->s_own;
+  order_after_dev_push(h);
   int rc;
   const PushGeom g = push_geom(h, n);
   if (n > kBulkRows) {  // bulk: no pinned staging, straight 2-D copies from/to the caller's buffers
@@ -1050,6 +1068,7 @@ extern "C" int hga_stream_push_packet(hga_handle* h, const void* packet_host, in
   if (n < 1 || n > kBulkRows || n + h->overlap > h->cap_rows) return fail(HGA_ERR_INVALID, "packet of %lld samples outside [1, min(max_push_rows, %lld)]", (long long)n, (long long)kBulkRows);
   CU(cudaSetDevice(h->cfg.device));
   cudaStream_t st = h->s_own;
+  order_after_dev_push(h);
   const PushGeom g = push_geom(h, n);
   const size_t in_bytes = (size_t)n * C * 4, out_bytes = (size_t)std::max<int64_t>(1, g.frames) * C * 8;
   if ((rc = h->pin_in.reserve(in_bytes)) || (rc = h->pin_out.reserve(out_bytes)) || (rc = h->xdev.reserve(in_bytes)) ||

@@ -386,6 +386,30 @@ def test_streaming_matches_oracle_unit(chunks):
     assert np.array_equal(ex.fh_state, ref_ex.fh_state)
 
 
+def test_streaming_device_and_host_pushes_interleave(torch):
+    """Device pushes run on the caller's stream, host pushes on the handle's own: the library orders one behind the other
+    (no synchronise in between here), so a mixed sequence equals the oracle's packet-by-packet result."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, C, n, P = 1000, 64, 10, 120
+    x = O.synthetic_ecog(n * P, C, fs, "ecog", session=9)
+    ref_ex = O.HighGammaExtractor(fs, C, log_power=O.compute_log_power_features)
+    eng = HgaEngine(fs, C, precision="exact")
+    xd = torch.from_numpy(x).cuda()
+    side = torch.cuda.Stream()
+    got, want = [], []
+    for i in range(P):
+        want.append(ref_ex.extract_features(x[i * n:(i + 1) * n]))
+        if i % 3 == 1:
+            with torch.cuda.stream(side):                    # a non-default caller stream, never synchronised by the test
+                got.append(eng.push(xd[i * n:(i + 1) * n]))
+        else:
+            got.append(eng.push(x[i * n:(i + 1) * n]))
+    torch.cuda.synchronize()
+    for g, w in zip(got, want):
+        g = g.cpu().numpy() if hasattr(g, "cpu") else g
+        assert g.shape == w.shape and _err(g, w)[0] <= 10 * TOL_EXACT
+
+
 def test_streaming_long_lived_handle_10500_packets():
     """BASELINE config 3 / SURVEY 8d: >= 10 500 ten-sample pushes on ONE handle (105 s of signal).  Frames within the
     reference-order bound of the oracle's filtering + framing of the whole signal (streaming == offline on
