@@ -56,6 +56,7 @@ SIGNATURES = {
     "hga_log_power": (C.c_int, [_i32, _vp, _i64, _i64, _i32, _i64, _i64, _i32, _i32, _vp, _vp, _dbl, _vp, _vp, _vp, _i64, _vp]),
     "hga_zscore": (C.c_int, [_i32, _vp, _i64, _i32, _i64, _vp, _vp, _vp, _i64, _vp]),
     "hga_stats_accumulate": (C.c_int, [_i32, _vp, _i64, _i32, _i64, _vp, _vp]),
+    "hga_stats_accumulate_static": (C.c_int, [_i32, _vp, _i64, _i32, _i64, _vp, _vp]),
     "hga_stats_merge": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _vp]),
     "hga_stats_finalize": (C.c_int, [_i32, _vp, _i32, _vp, _vp, _vp]),
     "hga_stats_merge_days": (C.c_int, [_i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),

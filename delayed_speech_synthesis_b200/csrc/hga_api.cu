@@ -1251,6 +1251,59 @@ extern "C" int hga_stats_accumulate(int32_t device, const double* feats_dev, int
   LAUNCHED();
   return HGA_OK;
 }
+// ---- hga_stats_accumulate without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The block partials of k_stats_partial live in a file-scope device array instead of the grow-only DevBuf above.  Every GPU
+// that loads the library holds its 1 MiB until exit.  In host code the array's name is only a stand-in: its device address
+// is looked up once per device, with that device current (cudaGetSymbolAddress), and that pointer goes to the kernels.
+// All calls on a device share the array: calls that overlap on the GPU (different streams, no ordering) race on it.
+// Nothing in it has to start at zero: k_stats_partial writes every partial k_stats_merge reads (nby x 3 x C doubles), the
+// rest keeps whatever the last call left.
+constexpr size_t kStatsStaticDoubles = (1u << 20) / 8;   // 131 072 doubles = 1 MiB
+static __device__ __align__(256) double g_stats_static[kStatsStaticDoubles];
+static std::mutex g_stats_static_mu;
+static double* g_stats_static_ptr[64] = {};
+extern "C" int hga_stats_accumulate_static(int32_t device, const double* feats_dev, int64_t F, int32_t C, int64_t ld, double* acc_dev,
+                                           void* stream) {
+  if (!feats_dev || !acc_dev) return fail(HGA_ERR_INVALID, "null argument");
+  if (C < 1 || ld < C || F < 0) return fail(HGA_ERR_INVALID, "bad shape");
+  if (device < 0 || device >= 64) return fail(HGA_ERR_INVALID, "device ordinal %d outside [0, 64)", device);
+  if (hga_device_count() < 1) return fail(HGA_ERR_NO_DEVICE, "no CUDA device visible: libhga_b200 has no CPU fallback");
+  CU(cudaSetDevice(device));
+  int n_sm = 148;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+  // the same tiling as hga_stats_accumulate (same partials, same merge order: the two entry points return the same bits)
+  const int cg = (C + 31) / 32;
+  int64_t nby = std::max<int64_t>(1, std::min<int64_t>((int64_t)n_sm * 8 / cg, (std::max<int64_t>(F, 1) + 63) / 64));
+  nby = std::min<int64_t>(nby, 65535);
+  const int64_t rpb = (std::max<int64_t>(F, 1) + nby - 1) / nby;
+  nby = (std::max<int64_t>(F, 1) + rpb - 1) / rpb;
+  const size_t need = (size_t)nby * 3 * (size_t)C;
+  if (need > kStatsStaticDoubles)
+    return fail(HGA_ERR_INVALID, "hga_stats_accumulate_static: %lld row tiles x 3 x %d channels = %zu doubles of block partials exceed the static scratch of %zu "
+                "doubles (1 MiB; at most 43690 channels) - use hga_stats_accumulate", (long long)nby, C, need, kStatsStaticDoubles);
+  if (F == 0) return HGA_OK;
+  double* part = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_stats_static_mu);
+    if (!g_stats_static_ptr[device]) {   // set-up, once per device, with that device current
+      void* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, g_stats_static);
+      if (e != cudaSuccess || !p) {
+        cudaGetLastError();
+        return fail(HGA_ERR_CUDA, "cudaGetSymbolAddress(g_stats_static) failed on device %d: %s", device, cudaGetErrorString(e));
+      }
+      g_stats_static_ptr[device] = static_cast<double*>(p);
+    }
+    part = g_stats_static_ptr[device];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  k_stats_partial<<<dim3((unsigned)cg, (unsigned)nby), 256, 0, st>>>(feats_dev, F, C, ld, rpb, part);
+  LAUNCHED();
+  k_stats_merge<<<(C + 127) / 128, 128, 0, st>>>(acc_dev, part, (int)nby, C);
+  LAUNCHED();
+  return HGA_OK;
+}
 extern "C" int hga_stats_merge_days(int32_t device, const double* gathered_dev, int32_t n_src, int32_t n_days, int32_t C, double* mu_dev,
                                     double* sigma_dev, void* stream) {
   if (!gathered_dev || !mu_dev || !sigma_dev) return fail(HGA_ERR_INVALID, "null argument");

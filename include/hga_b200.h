@@ -185,6 +185,15 @@ int hga_stats_accumulate(int32_t device, const double* feats_dev, int64_t F, int
                          void* stream);
 int hga_stats_merge(int32_t device, double* acc_a_dev, const double* acc_b_dev, int32_t count, int32_t C,
                     void* stream);
+/* hga_stats_accumulate that allocates nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same result bit for bit; the block partials go to a 1 MiB static device array instead of the library's
+ * grow-only scratch, so the call issues no cudaMalloc / cudaFree.  Limit: row tiles x 3 x C doubles <= 131072 (on a
+ * 148-SM device: any C up to 43690 channels); larger shapes return HGA_ERR_INVALID with the sizes in hga_last_error().
+ * Every call on a device shares the array (it keeps the last call's partials; nothing needs clearing, every word read
+ * is written first): calls that overlap on the GPU - different streams without ordering - race on it. */
+int hga_stats_accumulate_static(int32_t device, const double* feats_dev, int64_t F, int32_t C, int64_t ld,
+                                double* acc_dev, void* stream);
 int hga_stats_finalize(int32_t device, const double* acc_dev, int32_t C, double* mu_dev, double* sigma_dev,
                        void* stream);
 /* The day-baseline exchange of a sharded corpus in one launch (prepare_corpus.py:183-199 over ranks): gathered_dev holds
