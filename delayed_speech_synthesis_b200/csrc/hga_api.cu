@@ -302,6 +302,7 @@ struct hga_handle {
   std::vector<int64_t> lane_key;
   DevBuf lane_work, lane_fix, lane_segs, lane_order, lane_counter, lane_y, lane_bs, lane_E, lane_S0, lane_M;
   bool lane_use_M = false;
+  int lane_window = 0;   // > 0: windowed parallel carry (lane_carry_window), else the per-segment chain
   int n_sm = 0;
   int warmup = 0;
   int overlap = 0;   // L - hop
@@ -622,12 +623,18 @@ static int lane_prepare(hga_handle* h, int n_seg, const int64_t* seg_start, cons
         (rc = h->lane_segs.reserve(std::max<size_t>(1, p.segs.size()) * sizeof(LaneCarrySeg))) || (rc = h->lane_order.reserve(std::max<size_t>(1, p.order.size()) * 2 * sizeof(int))) ||
         (rc = h->lane_counter.reserve(16)) || (rc = h->lane_y.reserve(std::max<size_t>(16, (size_t)p.y_rows * CP * ysz))) ||
         (rc = h->lane_bs.reserve(std::max<size_t>(16, (size_t)p.bs_rows * CP * 8))) || (rc = h->lane_E.reserve(std::max<size_t>(16, nf * kLaneState * CP * 8))) ||
-        (rc = h->lane_M.reserve(kLaneState * kLaneState * 8)))
+        (rc = h->lane_M.reserve(2 * kLaneState * kLaneState * 8)))
       return rc;
     // the carry is propagated across a chunk only where it survives it (chunks shorter than the carry's reach)
     std::vector<double> M(kLaneState * kLaneState);
     const double tol = h->cfg.warmup_tol > 0 ? h->cfg.warmup_tol : (h->cfg.precision == HGA_PREC_F64 ? 1e-11 : h->cfg.precision == HGA_PREC_F32 ? 1e-6 : 1e-7);
     h->lane_use_M = nf > 1 && lane_transition(h->lk, p.Lc, M.data()) > 1e-3 * tol;
+    h->lane_window = h->lane_use_M ? lane_carry_window(M.data(), 1e-3 * tol) : 0;
+    if (h->lane_use_M) {   // M, then its transpose
+      M.resize(2 * kLaneState * kLaneState);
+      for (int i = 0; i < kLaneState; ++i)
+        for (int j = 0; j < kLaneState; ++j) M[kLaneState * kLaneState + j * kLaneState + i] = M[i * kLaneState + j];
+    }
     if (h->lane_use_M && (rc = h->lane_S0.reserve(nf * kLaneState * CP * 8))) return rc;
     CU(cudaMemcpyAsync(h->lane_work.p, p.work.data(), p.work.size() * sizeof(LaneWork), cudaMemcpyHostToDevice, st));
     if (nf) CU(cudaMemcpyAsync(h->lane_fix.p, p.fix.data(), nf * sizeof(LaneFix), cudaMemcpyHostToDevice, st));
@@ -662,6 +669,8 @@ static LaneDev lane_dev(const hga_handle* h) {
   d.E = h->lane_E.as<double>();
   d.S0 = h->lane_S0.as<double>();
   d.M = h->lane_use_M ? h->lane_M.as<double>() : nullptr;
+  d.MT = h->lane_use_M ? h->lane_M.as<double>() + kLaneState * kLaneState : nullptr;
+  d.carry_window = h->lane_window;
   d.subs = h->lane_subs.as<LaneSub>();
   d.n_sub = h->lane_nsub;
   d.P = h->lane_P.as<double>();

@@ -138,6 +138,27 @@ inline double lane_transition(const LaneConst& k, int64_t n, double* M) {
   return mx;
 }
 
+// End states a chunk's start state has to sum: the smallest w with max |M^w| <= thresh, M = A^Lc (the first dropped term of
+// s0(f) = sum_p M^p e(f - p)); 0 when the powers have not decayed after `cap` products (then the sequential chain is used).
+constexpr int kLaneCarryWindowMax = 8;
+inline int lane_carry_window(const double* M, double thresh, int cap = kLaneCarryWindowMax) {
+  constexpr int N = kLaneState;
+  std::vector<double> Pw(M, M + N * N), T(N * N);
+  for (int w = 1; w <= cap; ++w) {
+    double mx = 0.0;
+    for (int i = 0; i < N * N; ++i) mx = std::max(mx, std::fabs(Pw[i]));
+    if (mx <= thresh) return w;
+    for (int i = 0; i < N; ++i)
+      for (int j = 0; j < N; ++j) {
+        double acc = 0.0;
+        for (int l = 0; l < N; ++l) acc += Pw[i * N + l] * M[l * N + j];
+        T[i * N + j] = acc;
+      }
+    Pw.swap(T);
+  }
+  return 0;
+}
+
 // Pieces of the head fix-up (k_lane_fix) and their start-state operators: the staged zero-input evolution of the 32 unit
 // states, sampled where a piece starts.  Pieces are cut to roughly equal operation counts so that they finish together;
 // every piece but the first starts kLaneNB - 1 hop blocks before the first frame it finishes.
@@ -320,6 +341,7 @@ inline void lane_plan(const LaneConst& k, int hop, int C, int cw, int n_seg, con
         f.n_frames = all_head ? nblk : Kd / hop + (kLaneNB - 1);
         f.next_fix = (all_head && j + 1 < nc) ? (int32_t)p.fix.size() + 1 : -1;
         f.first = j == 1;
+        f.pos = (int32_t)(j - 1);
         f.head_off = p.y_rows;
         f.bs_off = p.bs_rows;
         p.y_rows += f.head_rows;
@@ -365,6 +387,8 @@ struct LaneDev {  // device copies of a LanePlan and the scratch it needs (owned
   double* E = nullptr;    // plan.fix.size() * 32 * CP
   double* S0 = nullptr;   // same size (only used when the chunk transition does not underflow)
   const double* M = nullptr;  // 32 x 32 chunk transition, or nullptr when it underflows (chunks longer than the carry)
+  const double* MT = nullptr; // M transposed (k_lane_carry_win); used when carry_window > 0
+  int carry_window = 0;       // > 0: every start state sums the last carry_window end states, all pairs in parallel
   const LaneSub* subs = nullptr;  // LaneFixPlan (per handle)
   int n_sub = 0;
   const double* P = nullptr;
@@ -419,7 +443,12 @@ inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev&
   const double* s0 = d.E;
   if (d.M) {
     const int warps = (int)p.segs.size() * C;
-    k_lane_carry<<<(warps + 3) / 4, 128, 0, st>>>(d.E, d.S0, d.M, d.segs, (int)p.segs.size(), C, CP);
+    if (d.MT && d.carry_window > 0) {
+      const int64_t pairs = (int64_t)n_fix * C;
+      k_lane_carry_win<<<(unsigned)((pairs + 3) / 4), 128, 0, st>>>(d.E, d.S0, d.MT, d.fix, n_fix, C, CP, d.carry_window);
+    } else {
+      k_lane_carry<<<(warps + 3) / 4, 128, 0, st>>>(d.E, d.S0, d.M, d.segs, (int)p.segs.size(), C, CP);
+    }
     s0 = d.S0;
     ++launches;
   }

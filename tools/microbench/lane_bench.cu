@@ -154,6 +154,14 @@ static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, s
   std::vector<double> M(kLaneState * kLaneState);
   const double mx = lane_transition(k, p.Lc, M.data());
   dp.d.M = mx > 1e-3 * tol ? dp.up(M) : nullptr;   // the carry is only propagated across a chunk when it survives it
+  if (dp.d.M) {
+    std::vector<double> MT(M.size());
+    for (int i = 0; i < kLaneState; ++i)
+      for (int j = 0; j < kLaneState; ++j) MT[j * kLaneState + i] = M[i * kLaneState + j];
+    dp.d.MT = dp.up(MT);
+    dp.d.carry_window = lane_carry_window(M.data(), 1e-3 * tol);
+    if (verbose) printf("  carry window %d\n", dp.d.carry_window);
+  }
   if (verbose)
     printf("  plan: Lc=%lld chunks=%zu fixups=%zu head rows=%lld (%.1f MB) carry rows=%d pieces=%d |A^Lc|max=%.2e%s\n", (long long)p.Lc, p.work.size(),
            p.fix.size(), (long long)p.y_rows, (double)p.y_rows * CP * ysize / 1e6, lane_carry_rows(k), dp.d.n_sub, mx, dp.d.M ? "" : " (underflows: no propagation)");
