@@ -342,6 +342,50 @@ def device_rate(torch, eng, x, mu, sigma, steps, warm=3):
     return ms, out
 
 
+def chain_side(torch, dev, local, steps, hbm_peak):
+    """K2 through the reference's pre-transform chain (prepare_corpus.py:152-160: select both grids -> per-grid common average
+    -> select the speech grid; 129 raw columns -> 64 channels), packed float32: the chain inside the extraction kernel's load
+    stage (hga_extract_offline_mapped) against the same two launches as separate passes."""
+    from delayed_speech_synthesis_b200 import transforms as TR
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, c_raw, C, secs = 1000, 129, 64, 3600
+    T = fs * secs
+    x = make_recording(torch, dev, T, c_raw, fs, 4242)
+    x += torch.linspace(-500.0, 500.0, c_raw, dtype=torch.float64, device=dev)     # per-channel offsets, as raw counts x gain have
+    layout = np.arange(128) + 1
+    grids = [np.flip(layout[:64].reshape(8, 8), axis=0), layout[64:].reshape(8, 8)]
+    pre = [TR.ChannelSelection(np.arange(128)), TR.CommonAverageReferencing([19, 38, 77], grids, layout), TR.ChannelSelection(np.arange(64, 128))]
+    cmap = TR.ChannelMap(TR.fold(pre, c_raw), local)
+    eng = HgaEngine(fs, C, precision="f32", device=local)
+    F = eng.num_frames(T)
+    out = torch.empty((F, C), dtype=torch.float64, device=dev)
+    ms_f = time_steps(torch, lambda: eng.extract_offline_mapped(x, cmap, None, out=out), steps, 3)
+    fused = bool(eng.last_fused)
+    eng.set_timing(True)
+    eng.extract_offline_mapped(x, cmap, None, out=out)
+    main_ms = eng.last_kernel_split_ms()[0] if fused else None
+    eng.set_timing(False)
+    xm = torch.empty((T, C), dtype=torch.float64, device=dev)
+    out2 = torch.empty_like(out)
+
+    def two():
+        cmap.apply(x, out=xm)
+        eng.extract_offline(xm, None, out=out2)
+    ms_2 = time_steps(torch, two, steps, 3)
+    ms_map = time_steps(torch, lambda: cmap.apply(x, out=xm), steps, 1)
+    raw_bytes, out_bytes = T * c_raw * 8, F * C * 8
+    res = {"workload": f"k2 through the pre-transform chain: {c_raw} raw columns -> {C} channels x {secs} s @ {fs} Hz, float32 arithmetic",
+           "fused": fused, "ms_per_step": ms_f, "value": C * T / (ms_f / 1e3), "main_kernel_ms": main_ms,
+           "bytes_per_step": raw_bytes + out_bytes, "achieved_gbs": (raw_bytes + out_bytes) / (ms_f / 1e3) / 1e9,
+           "frac_hbm": (raw_bytes + out_bytes) / (ms_f / 1e3) / 1e9 / hbm_peak,
+           "two_pass": {"ms_per_step": ms_2, "chanmap_ms": ms_map, "value": C * T / (ms_2 / 1e3),
+                        "bytes_per_step": raw_bytes + 2 * T * C * 8 + out_bytes},
+           "max_abs_diff_fused_vs_two_pass": float((out - out2).abs().max().item()), "plan": eng.last_plan()}
+    del x, xm, out, out2, eng, cmap
+    torch.cuda.empty_cache()
+    return res
+
+
 def side_workload(torch, dev, local, name, precisions, steps, hbm_peak):
     """A further BASELINE configuration on the same GPU (short recordings, k4): channel-samples/s per precision."""
     from delayed_speech_synthesis_b200.engine import HgaEngine
@@ -654,6 +698,10 @@ def run_single(args):
                 sides[name] = side_workload(torch, dev, local, name, precs, st, hbm_peak)
             except Exception as exc:
                 sides[name] = {"error": repr(exc)}
+        try:
+            sides["k2_chain"] = chain_side(torch, dev, local, 10, hbm_peak)
+        except Exception as exc:
+            sides["k2_chain"] = {"error": repr(exc)}
         try:
             cp = Corpus(torch, dev, local, 0, 1, args.precision)
             ms5, exch = corpus_timed(torch, cp, 3, 1, torch.cuda.synchronize)

@@ -1497,6 +1497,59 @@ extern "C" int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int6
   return HGA_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ offline, channel map fused
+// extract_features with its pre-transform chain (local/units.py:147-152): the folded channel map runs inside the extraction
+// kernel's load stage (mapper warps, hga_kernels_lane.cuh) when the handle computes in packed float32 at hop 10 and the map
+// fits the kernel (raw rows of up to ~180 columns, at most 2 averaging groups); otherwise the map runs as a pass of its own
+// into scratch and the plain extraction follows.  Same results either way to the precision's tolerance.
+extern "C" int hga_extract_offline_mapped(hga_handle* h, hga_chanmap* map, const double* x_raw_dev, int64_t ldx, int32_t n_segments,
+                                          const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row, const double* mu_dev,
+                                          const double* sigma_dev, double* out_dev, int64_t ldo, void* stream, int32_t* fused) {
+  if (fused) *fused = 0;
+  if (!h || !map || !x_raw_dev || !out_dev || !seg_start || !seg_len || !out_row) return fail(HGA_ERR_INVALID, "null argument");
+  const int C = h->cfg.n_channels, L = h->cfg.frame_len, hop = h->cfg.hop;
+  if (map->c_out != C || map->device != h->cfg.device)
+    return fail(HGA_ERR_INVALID, "channel map yields %d columns on device %d, the extractor wants %d on device %d", map->c_out, map->device, C, h->cfg.device);
+  if (ldx < map->c_in || ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < number of columns");
+  if ((mu_dev == nullptr) != (sigma_dev == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
+  if (n_segments < 1) return HGA_OK;
+  for (int i = 0; i < n_segments; ++i)
+    if (seg_len[i] < L) return fail(HGA_ERR_INVALID, "segment %d has %lld rows < frame_len %d", i, (long long)seg_len[i], L);
+  CU(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t xlo = INT64_MAX, xhi = 0;
+  for (int i = 0; i < n_segments; ++i) { xlo = std::min(xlo, seg_start[i]); xhi = std::max(xhi, seg_start[i] + seg_len[i]); }
+  int rc;
+  if (h->cfg.precision == HGA_PREC_F32 && h->lane_ok && hop == 10 && h->nb > 0) {
+    if ((rc = lane_prepare(h, n_segments, seg_start, seg_len, out_row, xlo, st))) return rc;
+    LaneMapDev m;
+    m.raw = x_raw_dev + xlo * ldx;
+    m.ld_raw = ldx;
+    m.raw_rows = xhi - xlo;
+    m.C_in = map->c_in;
+    m.n_groups = map->n_groups;
+    m.n_idx = map->n_idx;
+    m.sel = map->sel; m.grp = map->grp; m.gptr = map->gptr; m.gidx = map->gidx; m.alpha = map->alpha; m.beta = map->beta;
+    LaneDev ld = lane_dev(h);
+    h->timed_main = false;
+    if (h->timing) { CU(cudaEventRecord(h->ev0, st)); ld.ev_main = h->ev_main; }
+    const int n = lanes_launch_map_t<LaneF32, 10, 20, 2, 2, 2, 3, 5>(h->lk, h->lane_plan_host, ld, m, C, mu_dev, sigma_dev, out_dev, ldo, h->n_sm, st);
+    if (n == -1) return fail(HGA_ERR_CUDA, "fused lane kernel launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (n > 0) {
+      g_launches.fetch_add(n, std::memory_order_relaxed);
+      if (h->timing) { CU(cudaEventRecord(h->ev1, st)); h->timed = true; h->timed_main = true; }
+      if (fused) *fused = 1;
+      return HGA_OK;
+    }
+  }
+  // the map as a pass of its own over the rows in use, then the plain extraction
+  const int64_t ldp = (C + 1) / 2 * 2;
+  if ((rc = h->xpad.reserve((size_t)(xhi - xlo) * ldp * 8))) return rc;
+  if ((rc = hga_chanmap_apply(map, x_raw_dev + xlo * ldx, xhi - xlo, ldx, h->xpad.as<double>(), ldp, stream))) return rc;
+  return extract_offline_dev(h, h->xpad.as<double>() - xlo * ldp, ldp, n_segments, seg_start, seg_len, out_row, mu_dev, sigma_dev, out_dev, ldo, st, nullptr,
+                             nullptr);
+}
+
 // ------------------------------------------------------------------------------------------------ offline, host buffers
 // Upload x in time slabs on the copy stream; after each slab, launch the work items whose rows are resident; download
 // each group's frame rows on the handle's own stream while the next slab uploads.

@@ -453,8 +453,9 @@ inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev&
     ++launches;
   }
   constexpr int CPT = LaneFixOf<TY>::type::CPT;
-  const dim3 g1((unsigned)(n_fix * d.n_sub), (unsigned)((CP / CPT + 63) / 64));
-  k_lane_fix<TY, HOP><<<g1, 64, 0, st>>>(k, d.fix, d.subs, d.n_sub, d.P, C, CP, d.ybuf, s0, d.bs, mu, sigma, out, ldo);
+  const int thr = CP / CPT <= 32 ? 32 : 64;   // one warp per CTA when a row of the scratch has no more than 32 thread-columns (64 packed channels)
+  const dim3 g1((unsigned)(n_fix * d.n_sub), (unsigned)((CP / CPT + thr - 1) / thr));
+  k_lane_fix<TY, HOP><<<g1, thr, (size_t)kFixRingRows * thr * 8, st>>>(k, d.fix, d.subs, d.n_sub, d.P, C, CP, d.ybuf, s0, d.bs, mu, sigma, out, ldo);
   const dim3 g2((unsigned)n_fix, (unsigned)((C + 127) / 128));
   k_lane_fix_frames<<<g2, 128, 0, st>>>(k, d.fix, n_fix, C, CP, d.bs, mu, sigma, out, ldo);
   return launches + 2;
@@ -501,6 +502,56 @@ inline int lanes_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& 
   lane_fill_args(p, d, C, mu, sigma, out, ldo, prof, a);
   const int grid = std::max(1, std::min(n_sm, (a.n_items + NI - 1) / NI));
   kern<<<grid, 32 * NI * NS, SM::total, st>>>(k, a, tm);
+  if (d.ev_main) cudaEventRecord(d.ev_main, st);
+  const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
+  return cudaGetLastError() == cudaSuccess ? launches : -1;
+}
+
+// ---- fused channel map: the section-pipelined kernel with one mapper warp per item slot (k_hga_lanes<..., MAP = true>)
+struct LaneMapDev {
+  const double* raw = nullptr;   // raw row that LaneWork::x_row == 0 names
+  int64_t ld_raw = 0, raw_rows = 0;
+  int C_in = 0, n_groups = 0, n_idx = 0;
+  const int32_t *sel = nullptr, *grp = nullptr, *gptr = nullptr, *gidx = nullptr;
+  const double *alpha = nullptr, *beta = nullptr;
+};
+template <class P, int HOP, int TB, int NI, int NS, int NSLOT, int NL>
+inline size_t lanes_map_smem(int c_in, int depth) {
+  using SM = LanesSmem<32 * P::CPL, TB, NI, NS, NSLOT, NL>;
+  return (SM::total + 15) / 16 * 16 + LaneMapSmem::per_cta + (size_t)NI * (TB / HOP) * LaneMapSmem::per_mapper(HOP, c_in, depth);
+}
+// Returns the number of kernels launched, -1 on a CUDA error, -2 when the map does not fit the kernel (too wide a raw row,
+// too many groups): the caller then runs the channel map as a pass of its own.
+template <class P, int HOP, int TB, int NI, int NS, int NSLOT, int NL, int U>
+inline int lanes_launch_map_t(const LaneConst& k, const LanePlan& p, const LaneDev& d, const LaneMapDev& m, int C, const double* mu, const double* sigma,
+                              double* out, int64_t ldo, int n_sm, cudaStream_t st) {
+  constexpr size_t kMaxSmem = 232448;
+  int depth = kMapDepth;   // raw hop blocks in flight per mapper warp: 3 when they fit, else 2
+  if (lanes_map_smem<P, HOP, TB, NI, NS, NSLOT, NL>(m.C_in, depth) > kMaxSmem) depth = 2;
+  const size_t bytes = lanes_map_smem<P, HOP, TB, NI, NS, NSLOT, NL>(m.C_in, depth);
+  if (bytes > kMaxSmem || m.C_in > kMapMaxCols || m.n_groups > kMapMaxGroups || m.n_idx > kMapMaxIdx) return -2;
+  auto kern = k_hga_lanes<P, HOP, TB, NI, NS, NSLOT, NL, U, false, true>;
+  static bool attr_set[64] = {};
+  if (!lane_set_smem(kern, kMaxSmem, attr_set)) return -1;
+  LaneArgs a;
+  lane_fill_args(p, d, C, mu, sigma, out, ldo, nullptr, a);
+  a.raw = m.raw;
+  a.ld_raw = m.ld_raw;
+  a.raw_rows = m.raw_rows;
+  a.C_in = m.C_in;
+  a.n_groups = m.n_groups;
+  a.n_idx = m.n_idx;
+  a.map_depth = depth;
+  a.m_sel = m.sel;
+  a.m_grp = m.grp;
+  a.m_gptr = m.gptr;
+  a.m_gidx = m.gidx;
+  a.m_alpha = m.alpha;
+  a.m_beta = m.beta;
+  CUtensorMap unused;
+  memset(&unused, 0, sizeof unused);
+  const int grid = std::max(1, std::min(n_sm, (a.n_items + NI - 1) / NI));
+  kern<<<grid, 32 * (NI * NS + NI * (TB / HOP)), bytes, st>>>(k, a, unused);
   if (d.ev_main) cudaEventRecord(d.ev_main, st);
   const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
   return cudaGetLastError() == cudaSuccess ? launches : -1;

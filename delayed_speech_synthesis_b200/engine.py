@@ -183,6 +183,34 @@ class HgaEngine:
                                                  out.ctypes.data, out.strides[0] // 8))
         return out
 
+    def extract_offline_mapped(self, x_raw, chanmap, segments=None, mu=None, sigma=None, out=None):
+        """`extract_offline(chanmap(x_raw))` for a CUDA float64 (T, chanmap.spec.c_in) tensor of rows BEFORE the channel map
+        (HighGammaExtractor's pre_transform chain, local/units.py:147-152): with precision 'f32' at hop 10 the map runs inside
+        the extraction kernel's load stage and the mapped recording is never written.  Sets `self.last_fused`."""
+        torch = _torch()
+        if not isinstance(x_raw, torch.Tensor) or not x_raw.is_cuda or x_raw.dtype != torch.float64 or x_raw.dim() != 2 or x_raw.stride(1) != 1:
+            raise ValueError("raw input must be a CUDA float64 (T, C_in) tensor with unit column stride")
+        if x_raw.shape[1] != chanmap.spec.c_in:
+            raise ValueError(f"expected {chanmap.spec.c_in} raw columns, got {x_raw.shape[1]}")
+        if chanmap.spec.c_out != self.n_channels or chanmap.device != self.device:
+            raise ValueError("channel map output width / device do not match the engine")
+        start, length, frames, out_row = self._segments(x_raw.shape[0], segments)
+        total = int(sum(frames))
+        if out is None:
+            out = torch.empty((total, self.n_channels), dtype=torch.float64, device=x_raw.device)
+        mu_t = sg_t = None
+        if mu is not None:
+            mu_t = torch.as_tensor(mu, dtype=torch.float64, device=x_raw.device).reshape(-1).contiguous()
+            sg_t = torch.as_tensor(sigma, dtype=torch.float64, device=x_raw.device).reshape(-1).contiguous()
+        (_, ps), (_, pl), (_, po) = a1, a2, a3 = _vec_i64(start), _vec_i64(length), _vec_i64(out_row)
+        fused = C.c_int32(0)
+        check(self._lib.hga_extract_offline_mapped(self._h, chanmap._h, x_raw.data_ptr(), x_raw.stride(0), len(start), ps, pl, po,
+                                                   mu_t.data_ptr() if mu_t is not None else None,
+                                                   sg_t.data_ptr() if sg_t is not None else None,
+                                                   out.data_ptr(), out.stride(0), _stream_ptr(self.device), C.byref(fused)))
+        self.last_fused = bool(fused.value)
+        return out
+
     def extract_offline_raw(self, raw, chanmap, gain=None, segments=None, mu=None, sigma=None, out=None):
         """`extract_offline` of `chanmap(raw * gain)` for a HOST recording of raw amplifier counts (numpy int16 / int32 /
         float32 / float64, (T, chanmap.spec.c_in)): slabs are uploaded at the raw element size and expanded on the device

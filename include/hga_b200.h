@@ -237,6 +237,19 @@ int hga_extract_offline_raw_host(hga_handle* h, hga_chanmap* map, const void* x_
                                  const int64_t* out_row, const double* mu_host, const double* sigma_host, double* out_host,
                                  int64_t ldo);
 
+/* hga_extract_offline with the pre-transform chain inside the extraction kernel:
+ * `HighGammaExtractor.extract_features` applies `pre_transform` and hands the result to the filters
+ * (/root/reference/local/units.py:147-152; chains as wired in prepare_corpus.py:152-160).  x_raw_dev: float64 device rows
+ * [rows, ldx], map->c_in columns wide, BEFORE the channel map; segments are given in those rows; everything else as
+ * hga_extract_offline.  When the handle computes in packed float32 (HGA_PREC_F32) at hop 10 and the map fits the kernel
+ * (raw rows of up to ~180 columns, at most 2 averaging groups with 512 members together) the mapped recording never exists
+ * in memory: mapper warps form the kernel's input tiles from the raw rows (*fused = 1).  Otherwise the map runs as a pass
+ * of its own into scratch and the plain extraction follows (*fused = 0).  fused may be NULL. */
+int hga_extract_offline_mapped(hga_handle* h, hga_chanmap* map, const double* x_raw_dev, int64_t ldx, int32_t n_segments,
+                               const int64_t* seg_start, const int64_t* seg_len, const int64_t* out_row,
+                               const double* mu_dev, const double* sigma_dev, double* out_dev, int64_t ldo, void* stream,
+                               int32_t* fused);
+
 /* ---- introspection for bench.py / tests ------------------------------------------------------------------------- */
 /* Kernel launches issued through this library by the calling process since load (all handles). */
 int64_t hga_launch_count(void);
