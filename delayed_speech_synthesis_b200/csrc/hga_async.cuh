@@ -39,6 +39,9 @@ __device__ __forceinline__ void cp_async8(void* dst_smem, const void* src) {
 __device__ __forceinline__ void cp_async8_s(uint32_t dst_smem, const void* src) {   // shared address already converted
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst_smem), "l"(src) : "memory");
 }
+__device__ __forceinline__ void cp_async16_s(uint32_t dst_smem, const void* src) {  // both addresses 16-byte aligned
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }

@@ -133,3 +133,29 @@ def test_fused_many_short_segments_several_items_per_warp():
     got = eng.extract_offline_mapped(torch.from_numpy(raw).cuda(), TR.ChannelMap(TR.fold(pre, c_raw), 0), segs).cpu().numpy()
     assert eng.last_fused and got.shape == want.shape
     assert np.abs(got - want).max() <= TOL_F32
+
+
+def test_fused_padded_rows_last_rows_and_two_channel_groups_with_means():
+    """Raw rows with a leading dimension wider than the map reads (row-by-row copies instead of one span), a segment that
+    ends on the recording's last row (the mappers' look-ahead is clamped there), and a map that keeps both grids after the
+    common average: 128 output channels = two items per chunk, each reading means of both groups' tables."""
+    import torch
+    from delayed_speech_synthesis_b200 import transforms as TR
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T, c_raw = 1000, 33_333, 130
+    raw = O.synthetic_ecog(T, c_raw, fs, "ecog", session=56) + np.linspace(300.0, -200.0, c_raw)[None, :]
+    layout = np.arange(128) + 1
+    grids = [layout[:64].reshape(8, 8), np.flip(layout[64:].reshape(8, 8), axis=1)]
+    bad = [1, 64, 65, 128]
+    both = np.arange(2, 130)
+    appl, comp = O.car_masks(bad, grids, layout)
+    mapped = O.common_average_reference(O.select_columns(raw, both), appl, comp)
+    pre = [TR.ChannelSelection(both), TR.CommonAverageReferencing(bad, grids, layout)]
+    segs = [(0, 20_000), (20_000, T)]
+    want = _oracle_offline(mapped, fs, segments=segs)
+    wide = torch.full((T, c_raw + 6), float("nan"), dtype=torch.float64, device="cuda")
+    wide[:, :c_raw] = torch.from_numpy(raw).cuda()
+    eng = HgaEngine(fs, 128, precision="f32", device=0)
+    got = eng.extract_offline_mapped(wide[:, :c_raw], TR.ChannelMap(TR.fold(pre, c_raw), 0), segs).cpu().numpy()
+    assert eng.last_fused and np.isfinite(got).all()
+    assert np.abs(got - want).max() <= TOL_F32
