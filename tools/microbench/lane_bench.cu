@@ -386,7 +386,7 @@ int main(int argc, char** argv) {
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
     const int reps = 10;
-    for (double po : {14000.0, 10000.0, 7000.0, 20000.0, 28000.0}) {
+    for (double po : {14000.0, 12000.0, 16000.0, 18000.0, 20000.0, 24000.0}) {
       g_piece_ops = po;
 #define FIX_X(V, TOL, NAME)                                                                          \
   {                                                                                                  \
