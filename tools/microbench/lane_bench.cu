@@ -311,6 +311,9 @@ int main(int argc, char** argv) {
           expect(check_variant<OneStage<LaneF32, 10, 50, 4, 2, 5>>("f32 TB50 NW4 NS2 U5", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
           expect(check_variant<OneStage<LaneMix, 10, 50, 4, 2, 5>>("mix TB50 NW4 NS2 U5", co, fs, T, C, Lc, 1e-7, ref, x, dmu, dsig, n_sm), 5e-3);
           expect(check_variant<Staged<LaneF32, 10, 50, 2, 2, 2, 3, 5>>("f32 2-stage x2 TB50", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
+          // the same with looser carry tolerances: how the error at the seams grows with the dropped tail of the zero-input response
+          expect(check_variant<Staged<LaneF32, 10, 50, 2, 2, 2, 3, 5>>("f32 2-stage x2 TB50 tol 1e-5", co, fs, T, C, Lc, 1e-5, ref, x, dmu, dsig, n_sm), 5e-3);
+          expect(check_variant<Staged<LaneF32, 10, 50, 2, 2, 2, 3, 5>>("f32 2-stage x2 TB50 tol 1e-4", co, fs, T, C, Lc, 1e-4, ref, x, dmu, dsig, n_sm), 5e-3);
           expect(check_variant<Staged<LaneF32, 10, 40, 2, 4, 2, 2, 5>>("f32 4-stage x2 TB40", co, fs, T, C, Lc, 1e-6, ref, x, dmu, dsig, n_sm), 5e-3);
           expect(check_variant<Staged<LaneF64, 10, 50, 2, 4, 2, 2, 5>>("f64 4-stage x2 TB50", co, fs, T, C, Lc, 1e-11, ref, x, dmu, dsig, n_sm), 5e-9);
         }
