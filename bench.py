@@ -444,9 +444,15 @@ class Corpus:
     def accumulate(self, f):
         return self.ChannelStats(self.C, self.local).update(f).acc
 
+    def extract_stats(self, x):
+        st = self.ChannelStats(self.C, self.local)
+        self.eng.extract_offline_stats(x, st, None, out=self.out)
+        return st.acc
+
     def step(self, timings=None, on_features=None):
         return self.corpus.extract_corpus(K5_SESSIONS, self.day_of, self.baseline, self.session, self.extract, self.accumulate,
-                                          n_channels=self.C, device=self.local, on_features=on_features, timings=timings)
+                                          n_channels=self.C, device=self.local, on_features=on_features, timings=timings,
+                                          extract_stats=self.extract_stats)
 
     # ---- parity, outside the timed region
     def parity(self, dist):

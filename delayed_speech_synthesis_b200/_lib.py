@@ -63,6 +63,8 @@ SIGNATURES = {
     "hga_chanmap_create": (C.c_int, [_i32, _i32, _i32, _pi32, _pi32, _vp, _vp, _i32, _pi32, _pi32, C.POINTER(_vp)]),
     "hga_chanmap_destroy": (C.c_int, [_vp]),
     "hga_chanmap_apply": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _i64, _vp]),
+    "hga_extract_offline_stats": (C.c_int, [_vp, _vp, _i64, _i32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                            _vp, _vp, _vp, _i64, _vp, _vp, C.POINTER(C.c_int32)]),
     "hga_extract_offline_mapped": (C.c_int, [_vp, _vp, _vp, _i64, _i32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                              _vp, _vp, _vp, _i64, _vp, C.POINTER(C.c_int32)]),
     "hga_chanmap_apply_raw": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _i64, _vp, _i64, _vp]),

@@ -97,7 +97,7 @@ def _chan_merge(a, b):
 
 
 def extract_corpus(n_sessions: int, day_of, baseline_sessions, get_session, extract, accumulate, *, n_channels: int, device=None,
-                   group=None, on_features=None, timings: Optional[dict] = None):
+                   group=None, on_features=None, timings: Optional[dict] = None, extract_stats=None):
     """The reference's corpus build (prepare_corpus.py:179-236) over the ranks of a process group, one process per GPU:
 
       1. `ZScoresFromSyllableRepetitions` (:183-199): per day, (n, mean, M2) of the features of that day's baseline
@@ -111,7 +111,9 @@ def extract_corpus(n_sessions: int, day_of, baseline_sessions, get_session, extr
     get_session(s) -> the session's recording (device tensor).  extract(x, mu, sigma) -> (F, C) features (mu = None: raw
     log-power).  accumulate(features) -> (3, C) tensor (n, mean, M2).  on_features(s, features): what the caller does with
     a finished session (the reference writes an HDF5 file, :233-234).  timings: optional dict that receives CUDA events
-    bracketing the exchange (`exchange_events`) when the tensors live on a device.
+    bracketing the exchange (`exchange_events`) when the tensors live on a device.  extract_stats(x) -> (3, C): when given,
+    it replaces accumulate(extract(x, None, None)) for the baseline sessions (`HgaEngine.extract_offline_stats`: the
+    statistics leave the extraction kernels, the features are not read back).
     Returns (mu, sigma, slots): (n_days, C) tensors and the day -> row table."""
     import torch
     import torch.distributed as dist
@@ -125,7 +127,7 @@ def extract_corpus(n_sessions: int, day_of, baseline_sessions, get_session, extr
     acc = None
     for s in mine:
         if s in base:
-            a = accumulate(extract(get_session(s), None, None))
+            a = extract_stats(get_session(s)) if extract_stats is not None else accumulate(extract(get_session(s), None, None))
             if acc is None:
                 acc = torch.zeros((n_days, 3, n_channels), dtype=torch.float64, device=a.device)
             d = slots[day_of[s]]

@@ -271,9 +271,15 @@ static int lane_fix_only(int precision, int hop, const LaneConst& k, const LaneP
   return HGA_OK;
 }
 static int lane_launch(int precision, int hop, const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu,
-                       const double* sigma, double* out, int64_t ldo, int n_sm, cudaStream_t st) {
+                       const double* sigma, double* out, int64_t ldo, int n_sm, cudaStream_t st, bool stats = false) {
   int n = -1;
-  if (precision == HGA_PREC_F64) {
+  if (stats && precision == HGA_PREC_F32) {        // the same kernels, leaving (n, mean, M2) partials of the frames they emit
+    // (packed float32 only: there the float64 pipe is idle and the accumulation is free - K2: 1.289 ms against 1.268 ms without
+    // statistics and 1.493 ms with the separate pass; in the float64 kernels it competes with the filter for the same pipe and
+    // costs more than the second read it saves, tools/stats_ab.py)
+    n = hop == 10 ? lanes_launch_t<LaneF32, 10, 60, 2, 2, 2, 3, 5, false, true>(k, p, d, tm, C, mu, sigma, out, ldo, n_sm, st)
+                  : lanes_launch_t<LaneF32, 20, 60, 2, 2, 2, 3, 5, false, true>(k, p, d, tm, C, mu, sigma, out, ldo, n_sm, st);
+  } else if (precision == HGA_PREC_F64) {
     n = hop == 10 ? lanes_launch_t<LaneF64, 10, 80, 2, 2, 2, 3, 5>(k, p, d, tm, C, mu, sigma, out, ldo, n_sm, st)
                   : lanes_launch_t<LaneF64, 20, 80, 2, 2, 2, 3, 5>(k, p, d, tm, C, mu, sigma, out, ldo, n_sm, st);
   } else if (precision == HGA_PREC_F32) {
@@ -300,7 +306,7 @@ struct hga_handle {
   DevBuf lane_subs, lane_P;
   LanePlan lane_plan_host;
   std::vector<int64_t> lane_key;
-  DevBuf lane_work, lane_fix, lane_segs, lane_order, lane_counter, lane_y, lane_bs, lane_E, lane_S0, lane_M;
+  DevBuf lane_work, lane_fix, lane_segs, lane_order, lane_counter, lane_y, lane_bs, lane_E, lane_S0, lane_M, lane_st;
   bool lane_use_M = false;
   int lane_window = 0;   // > 0: windowed parallel carry (lane_carry_window), else the per-segment chain
   int n_sm = 0;
@@ -437,7 +443,7 @@ extern "C" int hga_destroy(hga_handle* h) {
   cudaSetDevice(h->cfg.device);
   drain_push(h);
   for (DevBuf* b : {&h->state, &h->framebuf, &h->state2, &h->framebuf2, &h->work, &h->segs, &h->ybuf, &h->stats_part, &h->seg_state, &h->seg_rem, &h->lane_subs, &h->lane_P, &h->lane_work, &h->lane_fix, &h->lane_segs, &h->lane_order, &h->lane_counter,
-                    &h->lane_y, &h->lane_bs, &h->lane_E, &h->lane_S0, &h->lane_M,
+                    &h->lane_y, &h->lane_bs, &h->lane_E, &h->lane_S0, &h->lane_M, &h->lane_st,
                     &h->xdev, &h->outdev, &h->mudev, &h->sigdev, &h->rawdev, &h->xpad})
     b->release();
   h->pin_in.release();
@@ -1494,6 +1500,60 @@ extern "C" int hga_chanmap_apply_host(hga_chanmap* m, const double* x_host, int6
   CU(cudaMemcpy2D(m->xdev.p, (size_t)m->c_in * 8, x_host, (size_t)ldx * 8, (size_t)m->c_in * 8, (size_t)T, cudaMemcpyHostToDevice));
   if ((rc = hga_chanmap_apply(m, m->xdev.as<double>(), T, m->c_in, m->odev.as<double>(), m->c_out, nullptr))) return rc;
   CU(cudaMemcpy2D(out_host, (size_t)ldo * 8, m->odev.p, (size_t)m->c_out * 8, (size_t)m->c_out * 8, (size_t)T, cudaMemcpyDeviceToHost));
+  return HGA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ offline + baseline statistics
+// The day-baseline flow of prepare_corpus.py:190-199 / baseline_offline.py:45-60 - extract the baseline recording's trials,
+// then mean / std over all their frames - in one pass: the kernels that emit frames (k_hga_lanes, k_lane_fix,
+// k_lane_fix_frames) also leave (n, mean, M2) of what they emitted, and one small kernel Chan-merges those partials into
+// acc in a fixed order.  The features are never read back.  Packed-float32 handles only (see lane_launch); every other handle
+// (EXACT, F64, MIXED, non-standard cascades, layouts the TMA cannot describe) extracts first and accumulates in a second pass.
+extern "C" int hga_extract_offline_stats(hga_handle* h, const double* x_dev, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
+                                         const int64_t* seg_len, const int64_t* out_row, const double* mu_dev, const double* sigma_dev,
+                                         double* out_dev, int64_t ldo, double* acc_dev, void* stream, int32_t* fused) {
+  if (fused) *fused = 0;
+  if (!h || !x_dev || !out_dev || !acc_dev || !seg_start || !seg_len || !out_row) return fail(HGA_ERR_INVALID, "null argument");
+  const int C = h->cfg.n_channels, L = h->cfg.frame_len, hop = h->cfg.hop;
+  if (ldx < C || ldo < C) return fail(HGA_ERR_INVALID, "leading dimension < n_channels");
+  if ((mu_dev == nullptr) != (sigma_dev == nullptr)) return fail(HGA_ERR_INVALID, "mu and sigma must both be given or both be NULL");
+  if (n_segments < 1) return HGA_OK;
+  for (int i = 0; i < n_segments; ++i)
+    if (seg_len[i] < L) return fail(HGA_ERR_INVALID, "segment %d has %lld rows < frame_len %d", i, (long long)seg_len[i], L);
+  CU(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  const bool lanes = h->cfg.precision == HGA_PREC_F32 && h->nb > 0 && choose_variant(h, x_dev, ldx, true) == 2;
+  if (lanes) {
+    int64_t xlo = INT64_MAX, xhi = 0;
+    for (int i = 0; i < n_segments; ++i) { xlo = std::min(xlo, seg_start[i]); xhi = std::max(xhi, seg_start[i] + seg_len[i]); }
+    if ((rc = lane_prepare(h, n_segments, seg_start, seg_len, out_row, xlo, st))) return rc;
+    const LanePlan& p = h->lane_plan_host;
+    const size_t CP = (size_t)p.groups * p.cw, n_items = p.work.size() * p.groups, nf = p.fix.size();
+    const size_t n_main = n_items * 3 * p.cw, n_fix = nf * h->lane_nsub * 3 * CP, n_seam = nf * 3 * CP;
+    if ((rc = h->lane_st.reserve(std::max<size_t>(16, (n_main + n_fix + n_seam) * 8)))) return rc;
+    CUtensorMap tm;
+    if ((rc = lane_tensor(h, x_dev, ldx, xlo, xhi, &tm))) return rc;
+    LaneDev ld = lane_dev(h);
+    ld.st_main = h->lane_st.as<double>();
+    ld.st_fix = ld.st_main + n_main;
+    ld.st_seam = ld.st_fix + n_fix;
+    if ((rc = lane_launch(h->cfg.precision, hop, h->lk, p, ld, tm, C, mu_dev, sigma_dev, out_dev, ldo, h->n_sm, st, true))) return rc;
+    k_lane_stats_merge<<<C, 128, 0, st>>>(acc_dev, ld.st_main, (int)p.work.size(), p.groups, p.cw, ld.st_fix, (int)(nf * h->lane_nsub), ld.st_seam,
+                                                   (int)nf, C, (int)CP);
+    LAUNCHED();
+    if (fused) *fused = 1;
+    return HGA_OK;
+  }
+  int64_t F = 0;
+  for (int i = 0; i < n_segments; ++i) F = std::max<int64_t>(F, out_row[i] + (seg_len[i] - L) / hop + 1);
+  if ((rc = extract_offline_dev(h, x_dev, ldx, n_segments, seg_start, seg_len, out_row, mu_dev, sigma_dev, out_dev, ldo, st, nullptr, nullptr))) return rc;
+  // second pass over every segment's frames (the out_row ranges need not tile one block)
+  for (int i = 0; i < n_segments; ++i) {
+    const int64_t nf = (seg_len[i] - L) / hop + 1;
+    if ((rc = hga_stats_accumulate(h->cfg.device, out_dev + out_row[i] * ldo, nf, C, ldo, acc_dev, stream))) return rc;
+  }
+  (void)F;
   return HGA_OK;
 }
 

@@ -455,6 +455,52 @@ __device__ __forceinline__ Moments chan_merge(Moments a, Moments b) {
   return Moments{n, fma(d, w, a.mean), a.m2 + b.m2 + d * d * a.n * w};
 }
 
+// Statistics that left the extraction kernels as partials (hga_extract_offline_stats): per channel, the (n, mean, M2) of
+// every (item), (fix-up, piece) and (seam) that emitted frames of it.  One warp per channel: lane l Chan-merges partials
+// l, l + 32, ... of the concatenated list in index order, a butterfly with the lower lane's moments first merges the 32
+// results (fixed shape: deterministic), lane 0 merges the total into acc (acc first).
+__global__ void __launch_bounds__(128) k_lane_stats_merge(double* __restrict__ acc, const double* __restrict__ st_main, int n_work, int groups, int cw,
+                                                          const double* __restrict__ st_fix, int n_fixpart, const double* __restrict__ st_seam, int n_seam,
+                                                          int C, int CP) {
+  // one CTA of four warps per channel: thread t merges partials t, t + 128, ... in index order, each warp folds its 32 results
+  // with the butterfly, thread 0 merges the four warp results in warp order
+  __shared__ Moments wsum[4];
+  const int c = blockIdx.x, t = threadIdx.x, lane = t & 31;
+  const int g = c / cw, cl = c - g * cw;
+  const int total = n_work + n_fixpart + n_seam;
+  Moments m{0.0, 0.0, 0.0};
+  for (int i = t; i < total; i += 128) {
+    const double* p;
+    size_t stride;
+    if (i < n_work) {
+      p = st_main + ((size_t)(i * groups + g) * 3) * cw + cl;
+      stride = (size_t)cw;
+    } else if (i < n_work + n_fixpart) {
+      p = st_fix + (size_t)(i - n_work) * 3 * CP + c;
+      stride = (size_t)CP;
+    } else {
+      p = st_seam + (size_t)(i - n_work - n_fixpart) * 3 * CP + c;
+      stride = (size_t)CP;
+    }
+    const double pn = p[0];
+    if (pn > 0.0) m = chan_merge(m, Moments{pn, p[stride], p[2 * stride]});
+  }
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    Moments other{__shfl_xor_sync(0xffffffffu, m.n, o), __shfl_xor_sync(0xffffffffu, m.mean, o), __shfl_xor_sync(0xffffffffu, m.m2, o)};
+    m = (lane & o) ? chan_merge(other, m) : chan_merge(m, other);
+  }
+  if (lane == 0) wsum[t >> 5] = m;
+  __syncthreads();
+  if (t == 0) {
+    Moments tot = chan_merge(chan_merge(wsum[0], wsum[1]), chan_merge(wsum[2], wsum[3]));
+    tot = chan_merge(Moments{acc[c], acc[C + c], acc[2 * (size_t)C + c]}, tot);
+    acc[c] = tot.n;
+    acc[C + c] = tot.mean;
+    acc[2 * (size_t)C + c] = tot.m2;
+  }
+}
+
 constexpr int kStatsRowsPerBlock = 8;
 __global__ void __launch_bounds__(256, 8) k_stats_partial(const double* __restrict__ f, int64_t F, int C, int64_t ld,
                                                        int64_t rows_per_block, double* __restrict__ part) {

@@ -397,6 +397,8 @@ struct LaneDev {  // device copies of a LanePlan and the scratch it needs (owned
   int n_items = -1;       // -1: all items of the plan
   bool skip_fix = false;
   cudaEvent_t ev_main = nullptr;  // when set: recorded right behind the main kernel (hga_last_kernel_split_ms)
+  // statistics partials of the STATS kernels: [items][3][cw], [fix-ups x pieces][3][CP], [fix-ups][3][CP]
+  double *st_main = nullptr, *st_fix = nullptr, *st_seam = nullptr;
 };
 
 typedef CUresult (*LaneEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -430,10 +432,11 @@ inline void lane_fill_args(const LanePlan& p, const LaneDev& d, int C, const dou
   a.counter = d.counter;
   a.order = d.order;
   a.prof = prof;
+  a.st_main = d.st_main;
 }
 // State carry, head fix-up and the frames touching the heads (after the main kernel, same stream).  Returns the number of
 // kernels launched.
-template <typename TY, int HOP>
+template <typename TY, int HOP, bool STATS = false>
 inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev& d, int C, const double* mu, const double* sigma, double* out, int64_t ldo,
                            cudaStream_t st) {
   const int n_fix = (int)p.fix.size();
@@ -455,9 +458,11 @@ inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev&
   constexpr int CPT = LaneFixOf<TY>::type::CPT;
   const int thr = CP / CPT <= 32 ? 32 : 64;   // one warp per CTA when a row of the scratch has no more than 32 thread-columns (64 packed channels)
   const dim3 g1((unsigned)(n_fix * d.n_sub), (unsigned)((CP / CPT + thr - 1) / thr));
-  k_lane_fix<TY, HOP><<<g1, thr, (size_t)kFixRingRows * thr * 8, st>>>(k, d.fix, d.subs, d.n_sub, d.P, C, CP, d.ybuf, s0, d.bs, mu, sigma, out, ldo);
+  if (STATS) cudaMemsetAsync(d.st_fix, 0, (size_t)n_fix * d.n_sub * 3 * CP * 8, st);   // pieces beyond a short head return without writing
+  k_lane_fix<TY, HOP, STATS><<<g1, thr, (size_t)kFixRingRows * thr * 8, st>>>(k, d.fix, d.subs, d.n_sub, d.P, C, CP, d.ybuf, s0, d.bs, mu, sigma, out, ldo,
+                                                                          STATS ? d.st_fix : nullptr);
   const dim3 g2((unsigned)n_fix, (unsigned)((C + 127) / 128));
-  k_lane_fix_frames<<<g2, 128, 0, st>>>(k, d.fix, n_fix, C, CP, d.bs, mu, sigma, out, ldo);
+  k_lane_fix_frames<<<g2, 128, 0, st>>>(k, d.fix, n_fix, C, CP, d.bs, mu, sigma, out, ldo, STATS ? d.st_seam : nullptr);
   return launches + 2;
 }
 template <class KernT>
@@ -490,12 +495,12 @@ inline int lane_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d
   return cudaGetLastError() == cudaSuccess ? launches : -1;
 }
 // The same with the section-pipelined kernel (NS warps per item, NI items per CTA).
-template <class P, int HOP, int TB, int NI, int NS, int NSLOT, int NL, int U, bool PROF = false>
+template <class P, int HOP, int TB, int NI, int NS, int NSLOT, int NL, int U, bool PROF = false, bool STATS = false>
 inline int lanes_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma,
                           double* out, int64_t ldo, int n_sm, cudaStream_t st, long long* prof = nullptr) {
   using SM = LanesSmem<32 * P::CPL, TB, NI, NS, NSLOT, NL>;
   static_assert(SM::total <= 232448, "more than 227 KB of shared memory");
-  auto kern = k_hga_lanes<P, HOP, TB, NI, NS, NSLOT, NL, U, PROF>;
+  auto kern = k_hga_lanes<P, HOP, TB, NI, NS, NSLOT, NL, U, PROF, false, STATS>;
   static bool attr_set[64] = {};
   if (!lane_set_smem(kern, SM::total, attr_set)) return -1;
   LaneArgs a;
@@ -503,7 +508,7 @@ inline int lanes_launch_t(const LaneConst& k, const LanePlan& p, const LaneDev& 
   const int grid = std::max(1, std::min(n_sm, (a.n_items + NI - 1) / NI));
   kern<<<grid, 32 * NI * NS, SM::total, st>>>(k, a, tm);
   if (d.ev_main) cudaEventRecord(d.ev_main, st);
-  const int launches = 1 + lane_launch_fix<typename P::TY, HOP>(k, p, d, C, mu, sigma, out, ldo, st);
+  const int launches = 1 + lane_launch_fix<typename P::TY, HOP, STATS>(k, p, d, C, mu, sigma, out, ldo, st);
   return cudaGetLastError() == cudaSuccess ? launches : -1;
 }
 

@@ -183,6 +183,33 @@ class HgaEngine:
                                                  out.ctypes.data, out.strides[0] // 8))
         return out
 
+    def extract_offline_stats(self, x, stats, segments=None, mu=None, sigma=None, out=None):
+        """`extract_offline` of a CUDA float64 (T, C) tensor that also merges the (n, mean, M2) of every frame it writes into
+        `stats` (an `ops.ChannelStats`): the day-baseline flow of prepare_corpus.py:190-199 in one pass.  With precision
+        'f32' the extraction kernels leave the statistics behind and the features are not read again (`self.last_fused`);
+        other handles extract, then accumulate."""
+        torch = _torch()
+        if not isinstance(x, torch.Tensor) or not x.is_cuda or x.dtype != torch.float64 or x.dim() != 2 or x.stride(1) != 1:
+            raise ValueError("device input must be a CUDA float64 (T, C) tensor with unit channel stride")
+        if x.shape[1] != self.n_channels or stats.n_channels != self.n_channels or stats.device != self.device:
+            raise ValueError(f"expected {self.n_channels} channels on device {self.device}")
+        start, length, frames, out_row = self._segments(x.shape[0], segments)
+        total = int(sum(frames))
+        if out is None:
+            out = torch.empty((total, self.n_channels), dtype=torch.float64, device=x.device)
+        mu_t = sg_t = None
+        if mu is not None:
+            mu_t = torch.as_tensor(mu, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
+            sg_t = torch.as_tensor(sigma, dtype=torch.float64, device=x.device).reshape(-1).contiguous()
+        (_, ps), (_, pl), (_, po) = a1, a2, a3 = _vec_i64(start), _vec_i64(length), _vec_i64(out_row)
+        fused = C.c_int32(0)
+        check(self._lib.hga_extract_offline_stats(self._h, x.data_ptr(), x.stride(0), len(start), ps, pl, po,
+                                                  mu_t.data_ptr() if mu_t is not None else None,
+                                                  sg_t.data_ptr() if sg_t is not None else None,
+                                                  out.data_ptr(), out.stride(0), stats.acc.data_ptr(), _stream_ptr(self.device), C.byref(fused)))
+        self.last_fused = bool(fused.value)
+        return out
+
     def extract_offline_mapped(self, x_raw, chanmap, segments=None, mu=None, sigma=None, out=None):
         """`extract_offline(chanmap(x_raw))` for a CUDA float64 (T, chanmap.spec.c_in) tensor of rows BEFORE the channel map
         (HighGammaExtractor's pre_transform chain, local/units.py:147-152): with precision 'f32' at hop 10 the map runs inside

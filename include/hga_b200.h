@@ -237,6 +237,18 @@ int hga_extract_offline_raw_host(hga_handle* h, hga_chanmap* map, const void* x_
                                  const int64_t* out_row, const double* mu_host, const double* sigma_host, double* out_host,
                                  int64_t ldo);
 
+/* hga_extract_offline that also accumulates the baseline statistics of the frames it writes: the day-baseline flow of
+ * /root/reference/prepare_corpus.py:190-199 and baseline_offline.py:45-60 (features of the baseline recording's trials,
+ * then np.mean / np.std over all frames) in one pass.  acc_dev is a (3, C) accumulator as for hga_stats_accumulate
+ * (zero-initialise to start; finish with hga_stats_finalize).  With HGA_PREC_F32 handles on layouts the lane kernels take,
+ * the kernels leave (n, mean, M2) partials of the frames they emit and one small kernel merges them in a fixed order
+ * (*fused = 1: the features are not read back; the accumulation runs on the otherwise idle float64 pipe); otherwise
+ * extraction and hga_stats_accumulate run one after the other behind the same call (*fused = 0: in the float64 kernels
+ * the accumulation would cost more than the second read).  fused may be NULL. */
+int hga_extract_offline_stats(hga_handle* h, const double* x_dev, int64_t ldx, int32_t n_segments, const int64_t* seg_start,
+                              const int64_t* seg_len, const int64_t* out_row, const double* mu_dev, const double* sigma_dev,
+                              double* out_dev, int64_t ldo, double* acc_dev, void* stream, int32_t* fused);
+
 /* hga_extract_offline with the pre-transform chain inside the extraction kernel:
  * `HighGammaExtractor.extract_features` applies `pre_transform` and hands the result to the filters
  * (/root/reference/local/units.py:147-152; chains as wired in prepare_corpus.py:152-160).  x_raw_dev: float64 device rows
