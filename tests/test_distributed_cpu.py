@@ -97,6 +97,12 @@ def _corpus_worker(rank, world, port, q):
     got = {}
     mu, sigma, slots = corpus.extract_corpus(len(sess), day_of, baseline, lambda s: sess[s], extract, accumulate, n_channels=C,
                                              on_features=lambda s, f: got.__setitem__(s, f.numpy().copy()))
+    # the one-pass baseline callback (HgaEngine.extract_offline_stats on a GPU) replaces accumulate(extract(x)): same statistics
+    calls = []
+    mu2, sigma2, _ = corpus.extract_corpus(len(sess), day_of, baseline, lambda s: sess[s], extract, None, n_channels=C,
+                                           extract_stats=lambda x: (calls.append(len(x)), accumulate(x))[1])
+    assert torch.equal(mu, mu2) and torch.equal(sigma, sigma2)
+    assert len(calls) == sum(1 for s in corpus.shard_weighted([2 if s in baseline else 1 for s in range(len(sess))], rank, world) if s in baseline)
     assert sorted(got) == corpus.shard_weighted([2 if s in baseline else 1 for s in range(len(sess))], rank, world)
     q.put((rank, mu.numpy().copy(), sigma.numpy().copy(), got))
     dist.barrier()
