@@ -1632,7 +1632,7 @@ static bool host_is_pinned(const void* p) {
 // ~10 GB/s, the PCIe link 50+
 static void host_rows_copy(unsigned char* dst, size_t dst_pitch, const unsigned char* src, size_t src_pitch, size_t row_bytes, int64_t rows) {
   const int64_t bytes = rows * (int64_t)row_bytes;
-  const int nt = (int)std::max<int64_t>(1, std::min<int64_t>({8, (int64_t)std::thread::hardware_concurrency(), bytes >> 22}));
+  const int nt = (int)std::max<int64_t>(1, std::min<int64_t>({16, (int64_t)std::thread::hardware_concurrency(), bytes >> 22}));
   auto part = [=](int64_t r0, int64_t r1) {
     if (dst_pitch == row_bytes && src_pitch == row_bytes) memcpy(dst + r0 * row_bytes, src + r0 * row_bytes, (size_t)(r1 - r0) * row_bytes);
     else for (int64_t r = r0; r < r1; ++r) memcpy(dst + r * dst_pitch, src + r * src_pitch, row_bytes);
