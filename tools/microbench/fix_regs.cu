@@ -6,7 +6,7 @@
 #include "hga_kernels_lane.cuh"
 namespace hga {
 template __global__ void k_lane_fix<float, 10>(const __grid_constant__ LaneConst, const LaneFix*, const LaneSub*, int, const double*, int, int, const void*, const double*, double*,
-                                               const double*, const double*, double*, int64_t);
+                                               const double*, const double*, double*, int64_t, double*);
 template __global__ void k_lane_fix<double, 10>(const __grid_constant__ LaneConst, const LaneFix*, const LaneSub*, int, const double*, int, int, const void*, const double*, double*,
-                                                const double*, const double*, double*, int64_t);
+                                                const double*, const double*, double*, int64_t, double*);
 }  // namespace hga
