@@ -24,9 +24,26 @@ def nvcc_path() -> str | None:
     return None
 
 
+HASH = PKG / "libhga_b200.so.srchash"   # written next to the library: which sources and flags it was built from
+
+
+def _source_hash() -> str:
+    import hashlib
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for p in sorted(SOURCES + HEADERS):
+        if p.exists():
+            h.update(p.name.encode())
+            h.update(p.read_bytes())
+    return h.hexdigest()
+
+
 def stale() -> bool:
+    """The library is missing or was built from other sources.  Decided on content (a copy of the tree to another machine
+    does not keep modification times in any useful order); modification times only when no hash was left by the build."""
     if not LIB.exists():
         return True
+    if HASH.exists():
+        return HASH.read_text().strip() != _source_hash()
     t = LIB.stat().st_mtime
     return any(p.stat().st_mtime > t for p in SOURCES + HEADERS if p.exists())
 
@@ -44,6 +61,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     (log / "ptxas.log").write_text(res.stdout + res.stderr)
     if res.returncode != 0:
         raise RuntimeError(f"nvcc failed:\n{res.stdout}\n{res.stderr}")
+    HASH.write_text(_source_hash() + "\n")
     if verbose:
         print(res.stderr)
     return LIB
