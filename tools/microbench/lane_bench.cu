@@ -226,6 +226,19 @@ static float run_variant(const char* name, const LaneConst& k, const LanePlan& p
     for (size_t i = 0; i < nprof / 3; ++i)
       if (h[3 * i + 2] > 0) { busy += h[3 * i]; wait += h[3 * i + 1]; tot += h[3 * i + 2]; maxtot = std::max(maxtot, (double)h[3 * i + 2]); ++n; }
     if (n) printf("    per-warp cycles (mean of %d): busy %.0f  tma-wait %.0f  total %.0f  (max total %.0f)\n", n, busy / n, wait / n, tot / n, maxtot);
+    if (NW == 4) {   // section-pipelined shapes (2 items x 2 stages): warp w of a CTA runs stage (w / 2 odd ? 1 - w % 2 : w % 2)
+      double sb[2] = {0, 0}, sw[2] = {0, 0};
+      int sn[2] = {0, 0};
+      for (size_t i = 0; i < nprof / 3; ++i)
+        if (h[3 * i + 2] > 0) {
+          const int w = (int)(i % NW), st = ((w / 2) & 1) ? 1 - (w % 2) : (w % 2);
+          sb[st] += h[3 * i];
+          sw[st] += h[3 * i + 1];
+          ++sn[st];
+        }
+      for (int st = 0; st < 2; ++st)
+        if (sn[st]) printf("    stage %d: busy %.0f  waiting %.0f\n", st, sb[st] / sn[st], sw[st] / sn[st]);
+    }
     cudaFree(dprof);
   }
   cudaEventDestroy(e0);
