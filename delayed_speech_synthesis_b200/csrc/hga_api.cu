@@ -732,6 +732,8 @@ static int extract_offline_dev(hga_handle* h, const double* x, int64_t ldx, int 
     CUtensorMap tm;
     if ((rc = lane_tensor(h, x, ldx, xlo, xhi, &tm))) return rc;
     LaneDev ld = lane_dev(h);
+    ld.x0 = x + xlo * ldx;
+    ld.ldx = ldx;
     h->timed_main = false;
     if (h->timing) { CU(cudaEventRecord(h->ev0, st)); ld.ev_main = h->ev_main; }
     if ((rc = lane_launch(h->cfg.precision, hop, h->lk, h->lane_plan_host, ld, tm, C, mu, sigma, out, ldo, h->n_sm, st))) return rc;
@@ -1535,6 +1537,8 @@ extern "C" int hga_extract_offline_stats(hga_handle* h, const double* x_dev, int
     CUtensorMap tm;
     if ((rc = lane_tensor(h, x_dev, ldx, xlo, xhi, &tm))) return rc;
     LaneDev ld = lane_dev(h);
+    ld.x0 = x_dev + xlo * ldx;
+    ld.ldx = ldx;
     ld.st_main = h->lane_st.as<double>();
     ld.st_fix = ld.st_main + n_main;
     ld.st_seam = ld.st_fix + n_fix;
@@ -1788,6 +1792,8 @@ static int extract_offline_host_impl(hga_handle* h, hga_chanmap* map, const void
     CUtensorMap tm;
     if ((rc = lane_tensor(h, xd, ldd, lo, hi, &tm))) return rc;
     LaneDev d = lane_dev(h);
+    d.x0 = xd + lo * ldd;
+    d.ldx = ldd;
     const int* order_time = h->lane_order.as<int>() + p.order.size();
     d.skip_fix = true;
     size_t next = 0;

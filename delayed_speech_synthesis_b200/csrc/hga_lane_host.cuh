@@ -325,6 +325,8 @@ inline void lane_plan(const LaneConst& k, int hop, int C, int cw, int n_seg, con
       w.rows = (int32_t)rows;
       w.blk0 = (int32_t)(t0 / hop);
       w.fresh = j == 0;
+      w.seg_row = (int32_t)(seg_start[i] - x_row_lo);
+      w.off_rows = T >= 3 ? 3 : 1;
       w.slot = j + 1 < nc ? (int32_t)p.fix.size() + (j > 0 ? 1 : 0) : -1;  // fix-up index of the successor
       w.tail_bs_off = -1;
       w.head_off = 0;
@@ -399,6 +401,10 @@ struct LaneDev {  // device copies of a LanePlan and the scratch it needs (owned
   cudaEvent_t ev_main = nullptr;  // when set: recorded right behind the main kernel (hga_last_kernel_split_ms)
   // statistics partials of the STATS kernels: [items][3][cw], [fix-ups x pieces][3][CP], [fix-ups][3][CP]
   double *st_main = nullptr, *st_fix = nullptr, *st_seam = nullptr;
+  // float32 arithmetic: the row of x that LaneWork::x_row == 0 names and its leading dimension (per-channel offset
+  // estimate, LaneF32::kOffset); nullptr: no offset is removed
+  const double* x0 = nullptr;
+  int64_t ldx = 0;
 };
 
 typedef CUresult (*LaneEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -433,6 +439,8 @@ inline void lane_fill_args(const LanePlan& p, const LaneDev& d, int C, const dou
   a.order = d.order;
   a.prof = prof;
   a.st_main = d.st_main;
+  a.x0 = d.x0;
+  a.ldx = d.ldx;
 }
 // State carry, head fix-up and the frames touching the heads (after the main kernel, same stream).  Returns the number of
 // kernels launched.
@@ -540,6 +548,7 @@ inline int lanes_launch_map_t(const LaneConst& k, const LanePlan& p, const LaneD
   if (!lane_set_smem(kern, kMaxSmem, attr_set)) return -1;
   LaneArgs a;
   lane_fill_args(p, d, C, mu, sigma, out, ldo, nullptr, a);
+  a.x0 = nullptr;   // the x rows exist only inside the kernel: the offset estimate forms its three samples from the raw rows
   a.raw = m.raw;
   a.ld_raw = m.ld_raw;
   a.raw_rows = m.raw_rows;

@@ -58,3 +58,30 @@ def test_statistics_of_z_scored_output_and_single_chunk():
     assert eng.last_fused and eng.last_plan()["carried"] == 0
     m, s = st.finalize()
     assert np.allclose(m, z.mean(0), rtol=1e-11, atol=1e-12) and np.allclose(s, z.std(0), rtol=1e-10)
+
+
+def test_statistics_at_full_k2_size_with_channel_gains_over_five_decades():
+    """K2 (128 ch x 3600 s @ 1 kHz), per-channel gains 1e-2 .. 1e3 so that the channel means of the log-power features spread
+    from -4.6 (the 0.01 floor inside the logarithm) to +12 around the kernels' fixed shift of 3: mu / sigma against a float64 two-pass mean / std of the features the
+    same call returned (computed on the device), and the frame count."""
+    import torch
+    from delayed_speech_synthesis_b200 import ops
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, C, T = 1000, 128, 3_600_000
+    g = torch.Generator(device="cuda").manual_seed(64)
+    x = torch.randn((T, C), dtype=torch.float64, device="cuda", generator=g)
+    x *= torch.logspace(-2, 3, C, dtype=torch.float64, device="cuda")
+    x += 5000.0                                                                    # amplifier offset: out of band, removed by the band-pass
+    eng = HgaEngine(fs, C, precision="f32", device=0)
+    st = ops.ChannelStats(C, 0)
+    feats = eng.extract_offline_stats(x, st)
+    assert eng.last_fused and eng.last_plan()["carried"] > 100
+    del x
+    mu, sg = st.finalize(as_numpy=False)
+    m_ref = feats.mean(0)
+    s_ref = (feats - m_ref).square().mean(0).sqrt()                                # np.std: population form
+    assert float(m_ref.max() - m_ref.min()) > 15.0
+    print('sigma range', float(s_ref.min()), float(s_ref.max()), 'max rel err', float(((sg - s_ref).abs() / s_ref).max()))
+    assert st.acc[0].cpu().numpy().tolist() == [float(feats.shape[0])] * C
+    assert torch.allclose(mu, m_ref, rtol=1e-12, atol=1e-12)
+    assert torch.allclose(sg, s_ref, rtol=1e-9)

@@ -167,6 +167,9 @@ static void upload_plan(const LaneConst& k, const LanePlan& p, int C, int hop, s
            p.fix.size(), (long long)p.y_rows, (double)p.y_rows * CP * ysize / 1e6, lane_carry_rows(k), dp.d.n_sub, mx, dp.d.M ? "" : " (underflows: no propagation)");
 }
 
+// the rows the last tensor map was built over (LaneDev::x0 / ldx: the float32 offset estimate of the staged kernel)
+static const double* g_x0 = nullptr;
+static int64_t g_ldx = 0;
 template <class P, int HOP, int TB, int NW, int NSLOT, int U>
 struct OneStage {
   using Pol = P;
@@ -182,7 +185,10 @@ struct Staged {
   static constexpr int hop = HOP, tb = TB, workers_per_sm = NI, prof_warps = NI * NS;
   template <bool PROF>
   static int launch(const LaneConst& k, const LanePlan& p, const LaneDev& d, const CUtensorMap& tm, int C, const double* mu, const double* sigma, double* out, int n_sm, long long* prof) {
-    return lanes_launch_t<P, HOP, TB, NI, NS, NSLOT, NL, U, PROF>(k, p, d, tm, C, mu, sigma, out, C, n_sm, 0, prof);
+    LaneDev dx = d;
+    dx.x0 = g_x0;
+    dx.ldx = g_ldx;
+    return lanes_launch_t<P, HOP, TB, NI, NS, NSLOT, NL, U, PROF>(k, p, dx, tm, C, mu, sigma, out, C, n_sm, 0, prof);
   }
 };
 
@@ -192,6 +198,8 @@ static float run_variant(const char* name, const LaneConst& k, const LanePlan& p
   using P = typename V::Pol;
   constexpr int HOP = V::hop, TB = V::tb, NW = V::prof_warps;
   CUtensorMap tm;
+  g_x0 = x;
+  g_ldx = ldx;
   if (lane_tensor_map(encode_fn(), x, ldx, C, T, 32 * P::CPL, TB, &tm) != CUDA_SUCCESS) { fprintf(stderr, "tensor map failed\n"); exit(2); }
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0));
@@ -265,6 +273,8 @@ static double check_variant(const char* name, const Coefs& co, int fs, int64_t T
   CK(cudaMalloc(&out, (size_t)F * C * 8));
   CK(cudaMemset(out, 0xff, (size_t)F * C * 8));  // NaN pattern: every frame must be written
   CUtensorMap tm;
+  g_x0 = x;
+  g_ldx = C;
   lane_tensor_map(encode_fn(), x, C, C, T, 32 * P::CPL, TB, &tm);
   if (V::template launch<false>(k, p, dp.d, tm, C, mu, sigma, out, n_sm, nullptr) < 0) { fprintf(stderr, "launch failed\n"); exit(2); }
   CK(cudaDeviceSynchronize());
@@ -414,6 +424,8 @@ int main(int argc, char** argv) {
     DevPlan dp;                                                                                      \
     upload_plan(k, p, C, hop, sizeof(typename V::Pol::TY), dp, false, TOL);                          \
     CUtensorMap tm;                                                                                  \
+    g_x0 = x;                                                                                        \
+    g_ldx = C;                                                                                       \
     lane_tensor_map(encode_fn(), x, C, C, T, 32 * V::Pol::CPL, V::tb, &tm);                          \
     V::template launch<false>(k, p, dp.d, tm, C, nullptr, nullptr, out, n_sm, nullptr);              \
     CK(cudaDeviceSynchronize());                                                                     \
