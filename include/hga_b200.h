@@ -50,8 +50,11 @@ enum hga_precision {
   /* float32 cascade arithmetic (two channels per register, fma.rn.f32x2) on the float64 input, float32 power sums / log /
    * z-score, same chunking and carry.  Offline extraction only (streaming pushes keep HGA_PREC_EXACT arithmetic).
    * |feature - reference| <= 1e-4 at 1 kHz, <= 5e-4 at 2 kHz on white / ECoG-like input (tests state it; typical 2e-5 /
-   * 1e-4).  Needs the standard cascade (8 + 8 unit-numerator sections, zi = sosfilt_zi), L = 5 hops, hop 10 or 20, x
-   * 16-byte aligned with an even leading dimension. */
+   * 1e-4).  A constant per (segment, channel) - the median of the segment's first three samples - is removed from x in float64
+   * before the conversion and folded into the start state, so an amplifier offset 1e4 .. 1e5 times the in-band amplitude
+   * costs the features nothing (same bound; 1e-3 inside the first 8 s of a segment, while the reference's own start
+   * transient decays from the offset's size).  Needs the standard cascade (8 + 8 unit-numerator sections,
+   * zi = sosfilt_zi), L = 5 hops, hop 10 or 20, x 16-byte aligned with an even leading dimension. */
   HGA_PREC_F32 = 2,
   /* float32 band-pass (poles <= 0.963, FMA pipe) + float64 notch (poles at 0.9976 - 0.9988, FP64 pipe), float64 power sums /
    * log / z-score.  |feature - reference| <= 5e-5 at 1 kHz, <= 2e-4 at 2 kHz (typical 1e-5 / 4e-5).  Same requirements
