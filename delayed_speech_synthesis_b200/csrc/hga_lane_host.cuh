@@ -453,12 +453,11 @@ inline int lane_launch_fix(const LaneConst& k, const LanePlan& p, const LaneDev&
   int launches = 0;
   const double* s0 = d.E;
   if (d.M) {
-    const int warps = (int)p.segs.size() * C;
     if (d.MT && d.carry_window > 0) {
       const int64_t pairs = (int64_t)n_fix * C;
       k_lane_carry_win<<<(unsigned)((pairs + 3) / 4), 128, 0, st>>>(d.E, d.S0, d.MT, d.fix, n_fix, C, CP, d.carry_window);
     } else {
-      k_lane_carry<<<(warps + 3) / 4, 128, 0, st>>>(d.E, d.S0, d.M, d.segs, (int)p.segs.size(), C, CP);
+      k_lane_carry<<<(unsigned)(p.segs.size() * ((C + kCarryCh - 1) / kCarryCh)), 32 * kCarryCh, 0, st>>>(d.E, d.S0, d.M, d.segs, (int)p.segs.size(), C, CP);
     }
     s0 = d.S0;
     ++launches;
