@@ -312,6 +312,24 @@ def test_offline_f32_weak_signal_on_a_large_offset(torch):
     assert d[800:].max() <= TOL_F32 and d[:800].max() <= 10 * TOL_F32
 
 
+@pytest.mark.parametrize("C", [6, 130])
+def test_offline_sequential_carry_ragged_channels_two_segments(C, torch):
+    """One-minute segments are cut into chunks of a few hundred rows, far shorter than the carry: the start states come from
+    the sequential chain (`k_lane_carry`: CTAs of 4 adjacent channels, cp.async ring of end-state tiles), here with a channel
+    count that is not a multiple of 4 or of a warp's channel group, and two segments of different chunk counts."""
+    from delayed_speech_synthesis_b200.engine import HgaEngine
+    fs, T = 1000, 100_000
+    x = O.synthetic_ecog(T, C, fs, "ecog", session=71) + np.linspace(-300.0, 300.0, C)[None, :]
+    segs = [(0, 61_003), (61_500, T)]
+    ref = _oracle_offline(x, fs, segments=segs)
+    for precision, tol in (("f64", TOL_F64), ("f32", TOL_F32)):
+        eng = HgaEngine(fs, C, precision=precision)
+        got = eng.extract_offline(torch.from_numpy(x).cuda(), segs).cpu().numpy()
+        plan = eng.last_plan()
+        assert plan["carried"] >= 40 and plan["chunk_rows"] < 2500, plan       # window far beyond 8 chunks: the sequential chain
+        assert got.shape == ref.shape and _err(got, ref)[0] <= tol, (precision, _err(got, ref), plan)
+
+
 def test_offline_exact_overlapping_segments(torch):
     """Trials closer than the 40 ms tail overlap in x (prepare_corpus.py:49); every one is filtered from its own fresh
     state, in every precision (the exact path used to share one scratch row per x row)."""
