@@ -12,8 +12,8 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
 LIB = ROOT / "delayed_speech_synthesis_b200" / "libhga_b200.so"
-WANT = [("k_hga_lanes<LaneF32, hop 10, TB 60, NI 2, NS 2>", "k_hga_lanesINS_7LaneF32ELi10E", "FFMA2"),
-        ("k_hga_lanes<LaneF64, hop 10, TB 80, NI 2, NS 2>", "k_hga_lanesINS_7LaneF64ELi10E", "DFMA"),
+WANT = [("k_hga_lanes<LaneF32, hop 10, TB 60, NI 2, NS 2>", "k_hga_lanesINS_7LaneF32ELi10ELi60ELi2ELi2ELi2ELi3ELi5ELb0ELb0ELb0E", "FFMA2"),
+        ("k_hga_lanes<LaneF64, hop 10, TB 80, NI 2, NS 2>", "k_hga_lanesINS_7LaneF64ELi10ELi80E", "DFMA"),
         ("k_lane_fix<float, hop 10>", "k_lane_fixIfLi10E", "FFMA2")]
 
 
